@@ -1,0 +1,192 @@
+/*
+ * go1sim.h -- C ABI of the B200-native batched Go1 simulator (libgo1sim.so / libgo1sim_f64.so).
+ *
+ * This is the drop-in boundary for the reference's environment hot path.  Every entry point
+ * names the reference interface it replaces (paths relative to the reference repo):
+ *
+ *   go1_create      <- Go1MujocoEnv.__init__ -> MujocoEnv.__init__ -> MjModel.from_xml_path
+ *                      (go1_mujoco_env.py:41-53) for N environments at once, and the worker
+ *                      construction of SubprocVecEnv (train.py:44-50)
+ *   go1_reset       <- VecEnv.reset() -> MujocoEnv.reset() -> Go1MujocoEnv.reset_model()
+ *                      (go1_mujoco_env.py:949-1001)
+ *   go1_step        <- SubprocVecEnv.step_async/step_wait -> Monitor.step -> Go1MujocoEnv.step
+ *                      (go1_mujoco_env.py:473-532: do_simulation = mj_step x frame_skip +
+ *                      mj_rnePostConstraint, _get_obs :915-947, _calc_reward :791-913,
+ *                      termination :487-498) + the worker's auto-reset / terminal_observation
+ *   go1_step_host   <- the same call with HOST numpy buffers (what SB3 hands to VecEnv.step)
+ *   go1_rollout     <- test_max_envs.py:129-138 (random-action stepping loop, steps/s)
+ *   go1_set_state / go1_get_state / go1_get_diag / go1_get_contacts
+ *                   <- direct reads/writes of mjData the reference does
+ *                      (data.qpos/qvel/qacc/qfrc_actuator/cfrc_ext/xpos/contact)
+ *   go1_set_attr_f32<- VecEnv.set_attr("_rand_power", v) (training_callback.py:64) and the
+ *                      constructor attributes of go1_mujoco_env.py:107-108
+ *
+ * Conventions: every function returns 0 on success or a negative GO1_E* code; the message is
+ * available from go1_last_error().  No exceptions cross the ABI.  One handle = one GPU = one host
+ * thread at a time.  Device-pointer arguments are raw CUDA device pointers (e.g. torch
+ * tensor.data_ptr()); `stream` is a cudaStream_t cast to void* (NULL = the handle's own stream).
+ * Per-environment numerical failure is not an error: the env is flagged, auto-reset and counted.
+ */
+#ifndef GO1SIM_H_
+#define GO1SIM_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GO1_OBS_DIM 48
+#define GO1_ACT_DIM 12
+#define GO1_NQ 19
+#define GO1_NV 18
+#define GO1_NBODY 14
+#define GO1_INFO_DIM 16
+#define GO1_MAX_CONTACTS 64
+
+enum {
+    GO1_OK = 0,
+    GO1_EINVAL = -1,      /* bad argument */
+    GO1_EMODEL = -2,      /* model blob rejected (format / unsupported topology or feature) */
+    GO1_ECUDA = -3,       /* CUDA runtime error */
+    GO1_ENOMEM = -4,
+    GO1_EUNSUPPORTED = -5 /* e.g. biped=1 */
+};
+
+/* Environment constants; zero-initialise then call go1_default_config() to obtain the
+ * reference's literals (go1_mujoco_env.py:64-150). */
+typedef struct Go1EnvConfig {
+    int32_t biped;                 /* go1_mujoco_env.py:41; must be 0 (biped terms: DESIGN.md "next") */
+    int32_t frame_skip;            /* :49  -> 10 */
+    int32_t max_episode_steps;     /* :64,:498 -> 6000 */
+    int32_t max_unhealthy_steps;   /* :130,:497 -> terminate at the 751st consecutive unhealthy step: 750 */
+    float rand_power;              /* :44,:974 */
+    float fallen_start_prob;       /* :953 -> 0.2 */
+    float desired_vel_min[3];      /* :107 */
+    float desired_vel_max[3];      /* :108 */
+    float reward_w[6];             /* :69-76  lin_vel, ang_vel, healthy, feet_airtime, recovery, get_up */
+    float cost_w[11];              /* :77-89  torque, vertical_vel, xy_angular_vel, action_rate, joint_limit,
+                                             joint_velocity, joint_acceleration, orientation, collision,
+                                             default_joint_position, unhealthy_state */
+    float healthy_z[2];            /* :118 */
+    float healthy_roll[2];         /* :120 (applied to qpos[4], as the reference does) */
+    float healthy_pitch[2];        /* :119 (applied to qpos[5]) */
+    float tracking_sigma;          /* :116 */
+    float obs_clip;                /* :150 */
+    float solver_tolerance;        /* <0: use the model's (MJCF <option tolerance>) */
+    int32_t solver_iterations;     /* <=0: use the model's */
+    int32_t reserved[8];
+} Go1EnvConfig;
+
+/* Full per-environment state for teacher-forced parity tests (doubles in both builds). */
+typedef struct Go1State {
+    double qpos[GO1_NQ];
+    double qvel[GO1_NV];
+    double qacc_warmstart[GO1_NV];
+    double last_action[GO1_ACT_DIM];
+    double feet_air_time[4];
+    double last_health_deviation[3];
+    double desired_velocity[3];
+    double episode_return;
+    int32_t last_contacts[4];
+    int32_t step;
+    int32_t unhealthy_steps;
+    int32_t reset_count;
+    int32_t bad_state;
+} Go1State;
+
+/* What mjData holds after do_simulation, as the reference reads it. */
+typedef struct Go1Diag {
+    double qacc[GO1_NV];
+    double qfrc_actuator[GO1_NV];
+    double qfrc_constraint[GO1_NV];
+    double cfrc_ext[GO1_NBODY][6];   /* [torque; force] about the robot COM, world axes (mj_rnePostConstraint) */
+    double trunk_xpos_z;             /* data.xpos[trunk][2] (start of the last substep) */
+    double subtree_com[3];
+    int32_t ncon;                    /* active contacts in the last substep */
+    int32_t solver_iter;             /* Newton iterations of the last substep */
+    int32_t solver_iter_total;       /* summed over the frame_skip substeps */
+    int32_t contact_overflow;        /* contacts dropped because a per-leg list was full */
+} Go1Diag;
+
+typedef struct Go1Contact {
+    int32_t geom;        /* MuJoCo geom id of the robot geom (geom1 is always the floor) */
+    int32_t dim;
+    double dist;
+    double pos[3];       /* world */
+    double force[6];     /* contact-frame force: normal, 2 tangents, torsion, 2 rolling */
+} Go1Contact;
+
+typedef struct Go1Stats {
+    double sum_reward;
+    double n_episodes;
+    double sum_episode_length;
+    double sum_episode_return;
+    double n_terminated;
+    double n_truncated;
+    double n_bad_state;
+    double env_steps;
+} Go1Stats;
+
+/* Policy for go1_rollout(action_mode=GO1_ACTION_POLICY): SB3 MlpPolicy actor 48-64-64-12 (tanh),
+ * a = clip(mu + exp(log_std) * eps, low, high). Row-major [out][in] weights (torch layout), device ptrs. */
+typedef struct Go1Policy {
+    const float* w0; const float* b0;    /* [64][48], [64] */
+    const float* w1; const float* b1;    /* [64][64], [64] */
+    const float* w2; const float* b2;    /* [12][64], [12] */
+    const float* log_std;                /* [12] or NULL for deterministic */
+} Go1Policy;
+
+enum { GO1_ACTION_RANDOM = 0, GO1_ACTION_POLICY = 1, GO1_ACTION_ZERO = 2 };
+
+typedef struct Go1Sim* go1_handle;
+
+void go1_default_config(Go1EnvConfig* cfg);
+int go1_precision_bits(void);                        /* 32 (product) or 64 (check build) */
+const char* go1_version(void);
+
+int go1_create(const void* model_blob, size_t nbytes, const Go1EnvConfig* cfg, int n_envs, int cuda_device,
+               uint64_t seed, uint64_t env_id_offset, go1_handle* out);
+int go1_destroy(go1_handle h);
+const char* go1_last_error(go1_handle h);            /* h may be NULL: last create error */
+
+int go1_num_envs(go1_handle h);
+int go1_action_bounds(go1_handle h, float* low12, float* high12);   /* actuator_ctrlrange */
+
+/* reset all envs (mask_dev NULL) or those with mask_dev[i] != 0; writes obs_dev[N][48] (may be NULL) */
+int go1_reset(go1_handle h, const uint8_t* mask_dev, float* obs_dev, void* stream);
+
+/* one control step for all envs, device buffers; asynchronous on `stream`.
+ * obs_dev[N][48] f32 (reset obs for done envs), rew_dev[N] f32, done_dev[N] u8, trunc_dev[N] u8
+ * (TimeLimit.truncated), terminal_obs_dev[N][48] (rows valid where done), info_dev[N][16] (nullable):
+ * x, y, 8 reward_info terms (go1_mujoco_env.py:860-867,908-909), episode return, episode length,
+ * health reason code, healthy flag, 2 spare. */
+int go1_step(go1_handle h, const float* actions_dev, float* obs_dev, float* rew_dev, uint8_t* done_dev,
+             uint8_t* trunc_dev, float* terminal_obs_dev, float* info_dev, void* stream);
+
+/* same with HOST buffers: H2D of actions, kernel, D2H of results, synchronous (the VecEnv path). */
+int go1_step_host(go1_handle h, const float* actions, float* obs, float* rew, uint8_t* done, uint8_t* trunc,
+                  float* terminal_obs, float* info);
+int go1_reset_host(go1_handle h, const uint8_t* mask, float* obs);
+
+/* device-resident stepping loop (throughput path): n_steps control steps with actions produced on the
+ * device; accumulates stats on the device and copies them to *out (nullable) at the end (synchronous). */
+int go1_rollout(go1_handle h, int n_steps, int action_mode, const Go1Policy* policy, Go1Stats* out, void* stream);
+/* elapsed device time (ms, CUDA events on the launch stream) and kernel launches of the last go1_rollout */
+int go1_last_rollout_timing(go1_handle h, float* ms, int* launches);
+
+int go1_set_state(go1_handle h, int env, const Go1State* s);
+int go1_get_state(go1_handle h, int env, Go1State* s);
+int go1_enable_diag(go1_handle h, int enable);       /* diag/contact capture costs HBM traffic: off by default */
+int go1_get_diag(go1_handle h, int env, Go1Diag* d);
+int go1_get_contacts(go1_handle h, int env, Go1Contact* buf, int cap, int* n);
+
+/* names: "rand_power", "fallen_start_prob", "desired_vel_min_x|y|z", "desired_vel_max_x|y|z" */
+int go1_set_attr_f32(go1_handle h, const char* name, float v);
+int go1_get_attr_f32(go1_handle h, const char* name, float* v);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GO1SIM_H_ */

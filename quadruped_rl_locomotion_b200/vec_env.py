@@ -1,0 +1,247 @@
+"""``Go1CudaVecEnv``: the reference's vectorised environment surface on top of the CUDA library.
+
+Drop-in for ``make_vec_env(Go1MujocoEnv, ..., vec_env_cls=SubprocVecEnv)`` (reference ``train.py:44-50``,
+``test_max_envs.py:35-41``): same constructor keywords as ``Go1MujocoEnv`` (``go1_mujoco_env.py:41``),
+same spaces (``Box(-inf, inf, (48,), float64)`` observations, ``Box(ctrlrange, float32)`` actions), and
+the SB3 2.3.0 ``VecEnv`` semantics the PPO loop relies on: auto-reset inside ``step``, the returned
+observation of a finished env is its reset observation, ``infos[i]["terminal_observation"]``,
+``infos[i]["TimeLimit.truncated"]``, and the ``Monitor`` record ``infos[i]["episode"] = {"r","l","t"}``.
+
+Host code only: every number comes from the CUDA kernels through ``go1_step_host`` (pinned staging,
+H2D actions -> one kernel -> D2H results).  If ``stable_baselines3`` / ``gymnasium`` are importable the
+class derives from SB3's ``VecEnv`` and uses gymnasium spaces; otherwise (this image) minimal
+stand-ins with the same attributes are used so the class is still importable and testable.
+"""
+from __future__ import annotations
+
+import os
+import time
+from typing import Any, List, Optional, Sequence
+
+import numpy as np
+
+from . import lib as _lib
+from .mjcf import Model, compile_mjcf
+
+try:  # pragma: no cover - not installed in the build image
+    from stable_baselines3.common.vec_env.base_vec_env import VecEnv as _SB3VecEnv
+    _HAVE_SB3 = True
+except Exception:  # noqa: BLE001
+    _SB3VecEnv = object
+    _HAVE_SB3 = False
+
+try:  # pragma: no cover
+    from gymnasium import spaces as _spaces
+    Box = _spaces.Box
+except Exception:  # noqa: BLE001
+    class Box:  # minimal gymnasium.spaces.Box stand-in
+        def __init__(self, low, high, shape=None, dtype=np.float32):
+            self.dtype = np.dtype(dtype)
+            self.shape = tuple(shape) if shape is not None else np.asarray(low).shape
+            self.low = np.broadcast_to(np.asarray(low, dtype=self.dtype), self.shape).copy()
+            self.high = np.broadcast_to(np.asarray(high, dtype=self.dtype), self.shape).copy()
+            self._rng = np.random.default_rng()
+
+        def seed(self, seed=None):
+            self._rng = np.random.default_rng(seed)
+            return [seed]
+
+        def sample(self):
+            return self._rng.uniform(self.low, self.high).astype(self.dtype)
+
+        def contains(self, x):
+            x = np.asarray(x)
+            return x.shape == self.shape and bool(np.all(x >= self.low) and np.all(x <= self.high))
+
+        def __eq__(self, other):
+            return (isinstance(other, Box) and self.shape == other.shape and self.dtype == other.dtype
+                    and np.array_equal(self.low, other.low) and np.array_equal(self.high, other.high))
+
+        def __repr__(self):
+            return f"Box({self.low.min()}, {self.high.max()}, {self.shape}, {self.dtype})"
+
+_MODEL_DIR = os.path.join(os.path.dirname(os.path.abspath(__file__)), "models")
+INFO_KEYS = ("linear_vel_tracking_reward", "reward_ctrl", "reward_survive", "recovery_reward", "get_up_reward",
+             "unhealthy_state_cost", "orientation_cost", "default_joint_position_cost")
+_REASONS = {0: "not_terminated", 1: "state_not_finite", 2: "unhealthy_z", 3: "unhealthy_roll", 4: "unhealthy_pitch"}
+
+
+def load_model_blob(ctrl_type: str = "torque", model_dir: Optional[str] = None) -> bytes:
+    """Compiled model for ``scene_<ctrl_type>.xml``.
+
+    ``model_dir`` = a directory with the reference's MJCF files (``unitree_go1/``): compiled on the fly with
+    :func:`compile_mjcf`; otherwise the blob shipped in ``models/`` (compiled from the reference's MJCF by
+    ``tests/golden/make_golden.py``) is used.
+    """
+    if ctrl_type not in ("torque", "position"):
+        raise ValueError(f"ctrl_type must be 'torque' or 'position', got {ctrl_type!r}")
+    if model_dir is not None:
+        return compile_mjcf(os.path.join(model_dir, f"scene_{ctrl_type}.xml")).to_blob()
+    path = os.path.join(_MODEL_DIR, f"go1_{ctrl_type}.go1m")
+    with open(path, "rb") as f:
+        return f.read()
+
+
+class Go1CudaVecEnv(_SB3VecEnv):
+    """N Go1 environments stepped by one CUDA kernel per control step."""
+
+    metadata = {"render_modes": []}
+
+    def __init__(self, num_envs: int, ctrl_type: str = "torque", biped: bool = False, rand_power: float = 0.0, *,
+                 device: int = 0, seed: int = 0, env_id_offset: int = 0, desired_velocity_min=(-0.5, 0.0, 0.0),
+                 desired_velocity_max=(0.5, 0.0, 0.0), model_dir: Optional[str] = None, precision: str = "f32",
+                 library: Optional[_lib.Go1Lib] = None, full_info: bool = False):
+        if biped:
+            raise NotImplementedError("biped=True is not implemented yet (DESIGN.md, 'next'); the CUDA path refuses it")
+        self._lib = library or _lib.Go1Lib(precision=precision)
+        blob = load_model_blob(ctrl_type, model_dir)
+        self.model = Model.from_blob(blob)
+        cfg = self._lib.default_config()
+        cfg.rand_power = float(rand_power)
+        for i in range(3):
+            cfg.desired_vel_min[i] = float(desired_velocity_min[i])
+            cfg.desired_vel_max[i] = float(desired_velocity_max[i])
+        self.sim = _lib.Sim(blob, num_envs, lib=self._lib, cfg=cfg, device=device, seed=seed, env_id_offset=env_id_offset)
+        lo, hi = self.sim.action_bounds()
+        observation_space = Box(low=-np.inf, high=np.inf, shape=(_lib.OBS_DIM,), dtype=np.float64)
+        action_space = Box(low=lo, high=hi, dtype=np.float32)
+        self.ctrl_type, self.biped, self._rand_power = ctrl_type, False, float(rand_power)
+        self.full_info = bool(full_info)
+        self.render_mode = None
+        n = int(num_envs)
+        self._actions = np.zeros((n, _lib.ACT_DIM), np.float32)
+        self._obs = np.zeros((n, _lib.OBS_DIM), np.float32)
+        self._tobs = np.zeros((n, _lib.OBS_DIM), np.float32)
+        self._rew = np.zeros(n, np.float32)
+        self._done = np.zeros(n, np.uint8)
+        self._trunc = np.zeros(n, np.uint8)
+        self._info = np.zeros((n, _lib.INFO_DIM), np.float32)
+        self._t_start = time.time()
+        self._empty_infos = [dict() for _ in range(n)]
+        if _HAVE_SB3:
+            super().__init__(n, observation_space, action_space)
+        else:
+            self.num_envs = n
+            self.observation_space = observation_space
+            self.action_space = action_space
+            self.reset_infos = [{} for _ in range(n)]
+
+    # ------------------------------------------------------------------ VecEnv API (SB3 2.3.0 base_vec_env.py)
+    def reset(self) -> np.ndarray:
+        self.sim.reset_host(self._obs)
+        self.reset_infos = [{} for _ in range(self.num_envs)]
+        return self._obs.astype(np.float64)
+
+    def step_async(self, actions: np.ndarray) -> None:
+        a = np.asarray(actions, dtype=np.float32)
+        if a.shape != (self.num_envs, _lib.ACT_DIM):
+            # the reference raises from MujocoEnv.do_simulation on a shape mismatch
+            raise ValueError(f"Action dimension mismatch. Expected {(self.num_envs, _lib.ACT_DIM)}, found {a.shape}")
+        np.copyto(self._actions, a)
+
+    def step_wait(self):
+        self.sim.step_host(self._actions, self._obs, self._rew, self._done, self._trunc, self._tobs, self._info)
+        dones = self._done.astype(bool)
+        infos = self._make_infos(dones)
+        return self._obs.astype(np.float64), self._rew.copy(), dones, infos
+
+    def step(self, actions: np.ndarray):
+        self.step_async(actions)
+        return self.step_wait()
+
+    def _make_infos(self, dones: np.ndarray) -> List[dict]:
+        """Per-env info dicts.  Done envs always get the keys SB3 reads; the per-step reward terms of
+        go1_mujoco_env.py:500-517,860-909 are materialised for every env only with ``full_info=True``
+        (16k dict constructions per step would dominate the step time otherwise)."""
+        if self.full_info:
+            infos = [self._info_dict(i) for i in range(self.num_envs)]
+        else:
+            infos = [dict() for _ in range(self.num_envs)] if dones.any() else self._empty_infos
+            if not dones.any():
+                return infos
+        now = time.time()
+        for i in np.flatnonzero(dones):
+            d = infos[i] if self.full_info else self._info_dict(i)
+            d["terminal_observation"] = self._tobs[i].astype(np.float64)
+            d["TimeLimit.truncated"] = bool(self._trunc[i])
+            d["episode"] = {"r": float(self._info[i, 10]), "l": int(self._info[i, 11]), "t": round(now - self._t_start, 6)}
+            infos[i] = d
+        return infos
+
+    def _info_dict(self, i: int) -> dict:
+        r = self._info[i]
+        d = {"x_position": float(r[0]), "y_position": float(r[1]), "distance_from_origin": float(np.hypot(r[0], r[1])),
+             "bipedal_success": False}
+        healthy = r[13] > 0.5
+        reason = _REASONS.get(int(r[12]), "not_terminated")
+        if self._done[i] and not self._trunc[i]:
+            d["termination_reason"] = f"prolonged_{reason}"
+        elif not healthy:
+            d["termination_reason"] = "unhealthy_state_active"
+        else:
+            d["termination_reason"] = "not_terminated"
+        for k, key in enumerate(INFO_KEYS):
+            d[key] = float(r[2 + k])
+        return d
+
+    def close(self) -> None:
+        self.sim.close()
+
+    def get_attr(self, attr_name: str, indices=None) -> List[Any]:
+        n = len(self._indices(indices))
+        if attr_name in ("_rand_power", "rand_power"):
+            return [self.sim.get_attr("rand_power")] * n
+        if attr_name == "_desired_velocity_min":
+            return [np.array([self.sim.get_attr(f"desired_vel_min_{c}") for c in "xyz"])] * n
+        if attr_name == "_desired_velocity_max":
+            return [np.array([self.sim.get_attr(f"desired_vel_max_{c}") for c in "xyz"])] * n
+        if hasattr(self, attr_name):
+            return [getattr(self, attr_name)] * n
+        raise AttributeError(attr_name)
+
+    def set_attr(self, attr_name: str, value: Any, indices=None) -> None:
+        """``training_env.set_attr("_rand_power", v)`` (training_callback.py:64) really reaches the simulator
+        (all envs share one value; per-index values are not supported)."""
+        if attr_name in ("_rand_power", "rand_power"):
+            self._rand_power = float(value)
+            self.sim.set_attr("rand_power", float(value))
+        elif attr_name in ("_desired_velocity_min", "_desired_velocity_max"):
+            tag = "min" if attr_name.endswith("min") else "max"
+            for c, v in zip("xyz", np.asarray(value, dtype=np.float64)):
+                self.sim.set_attr(f"desired_vel_{tag}_{c}", float(v))
+        else:
+            setattr(self, attr_name, value)
+
+    def env_method(self, method_name: str, *method_args, indices=None, **method_kwargs) -> List[Any]:
+        raise NotImplementedError(f"env_method({method_name!r}): there are no per-env Python objects behind this VecEnv")
+
+    def env_is_wrapped(self, wrapper_class, indices=None) -> List[bool]:
+        return [False] * len(self._indices(indices))
+
+    def seed(self, seed: Optional[int] = None) -> Sequence[Optional[int]]:
+        # the reference's resets ignore the gymnasium seed (unseeded np.random, go1_mujoco_env.py:953-959,1012);
+        # here the Philox key is fixed at construction.  action_space sampling is seeded like make_vec_env does.
+        self.action_space.seed(seed)
+        return [seed] * self.num_envs
+
+    def get_images(self):
+        return [None] * self.num_envs
+
+    def render(self, mode: Optional[str] = None):
+        return None  # graphics: unavailable on this box
+
+    def _indices(self, indices):
+        if indices is None:
+            return list(range(self.num_envs))
+        if isinstance(indices, int):
+            return [indices]
+        return list(indices)
+
+
+def make_go1_vec_env(n_envs: int = 12, env_kwargs: Optional[dict] = None, seed: int = 0, **kw) -> Go1CudaVecEnv:
+    """Signature-compatible replacement for the call at reference ``train.py:44-50``:
+    ``make_vec_env(Go1MujocoEnv, env_kwargs=..., n_envs=..., seed=..., vec_env_cls=SubprocVecEnv)``."""
+    env_kwargs = dict(env_kwargs or {})
+    env = Go1CudaVecEnv(n_envs, seed=seed, **env_kwargs, **kw)
+    env.seed(seed)
+    return env

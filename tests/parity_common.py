@@ -1,0 +1,121 @@
+"""Shared parity machinery: drives a ``libgo1sim`` build (real CUDA or the CPU SIMT emulation of the same
+source) through the C ABI, teacher-forced from golden states, and compares with the golden outputs
+(reference env code + oracle physics, ``tests/golden/make_golden.py``)."""
+from __future__ import annotations
+
+import os
+
+import numpy as np
+
+from quadruped_rl_locomotion_b200.lib import Sim
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+GOLDEN = os.path.join(ROOT, "tests", "golden")
+MODELS = os.path.join(ROOT, "quadruped_rl_locomotion_b200", "models")
+
+
+def model_blob(ctrl: str) -> bytes:
+    with open(os.path.join(MODELS, f"go1_{ctrl}.go1m"), "rb") as f:
+        return f.read()
+
+
+def load_trace(ctrl: str):
+    """Config-1 trace as (pre, post) dicts of equal length arrays."""
+    tr = np.load(os.path.join(GOLDEN, f"trace_{ctrl}.npz"))
+    n = len(tr["reward"])
+    pre = {k: tr[k][:n] for k in ("qpos", "qvel", "warm", "ep_step", "ep_last_action", "ep_feet_air_time",
+                                  "ep_last_contacts", "ep_desired_velocity", "ep_time_unhealthy", "ep_last_dev")}
+    post = {k: tr[k][1:n + 1] for k in ("qpos", "qvel", "warm", "ep_feet_air_time", "ep_last_contacts",
+                                        "ep_time_unhealthy", "ep_last_dev")}
+    for k in ("action", "qacc", "qfrc_actuator", "cfrc_ext", "trunk_z", "ncon", "con_geom", "con_dist", "con_fn", "obs",
+              "reward", "info", "healthy", "terminated", "truncated", "solver_iter"):
+        post[k] = tr[k][:n]
+    return pre, post
+
+
+def load_starts(ctrl: str):
+    st = np.load(os.path.join(GOLDEN, f"starts_{ctrl}.npz"))
+    pre = {k[4:]: st[k] for k in st.files if k.startswith("pre_")}
+    post = {k[5:]: st[k] for k in st.files if k.startswith("post_")}
+    for k in st.files:
+        if not k.startswith(("pre_", "post_")):
+            post[k] = st[k]
+    return pre, post
+
+
+def run_teacher_forced(lib, ctrl: str, pre, post, idx, capture_contacts: bool = False):
+    """Loads golden state idx[i] into env i, steps all envs ONCE with the golden actions; returns results."""
+    idx = np.asarray(idx)
+    n = len(idx)
+    sim = Sim(model_blob(ctrl), n, lib=lib, seed=7)
+    sim.enable_diag(True)
+    for e, t in enumerate(idx):
+        sim.set_state(
+            e, qpos=pre["qpos"][t], qvel=pre["qvel"][t], qacc_warmstart=pre["warm"][t],
+            last_action=pre["ep_last_action"][t], feet_air_time=pre["ep_feet_air_time"][t],
+            last_health_deviation=pre["ep_last_dev"][t], desired_velocity=pre["ep_desired_velocity"][t],
+            last_contacts=(pre["ep_last_contacts"][t] > 0).astype(int), step=int(pre["ep_step"][t]),
+            unhealthy_steps=int(round(float(pre["ep_time_unhealthy"][t]) / 0.02)), episode_return=0.0, bad_state=0)
+    actions = np.ascontiguousarray(post["action"][idx].astype(np.float32))
+    obs = np.zeros((n, 48), np.float32); rew = np.zeros(n, np.float32)
+    done = np.zeros(n, np.uint8); trunc = np.zeros(n, np.uint8)
+    tobs = np.zeros((n, 48), np.float32); info = np.zeros((n, 16), np.float32)
+    sim.step_host(actions, obs, rew, done, trunc, tobs, info)
+    out = dict(obs=obs, rew=rew, done=done, trunc=trunc, tobs=tobs, info=info, state=[], diag=[], contacts=[])
+    for e in range(n):
+        # a done env was auto-reset: its physics state is the reset state; parity on state is skipped for it
+        out["state"].append(sim.get_state(e))
+        out["diag"].append(sim.get_diag(e))
+        if capture_contacts:
+            out["contacts"].append(sim.get_contacts(e))
+    sim.close()
+    return out
+
+
+def rel_err(a, b, floor=1.0):
+    """max |a-b| / max(floor, max|b|): relative to the vector's scale, absolute below `floor`."""
+    a = np.asarray(a, dtype=np.float64); b = np.asarray(b, dtype=np.float64)
+    return float(np.abs(a - b).max() / max(floor, np.abs(b).max()))
+
+
+def compare(out, pre, post, idx):
+    """Returns dict of per-quantity worst errors over the batch + flag mismatches."""
+    idx = np.asarray(idx)
+    w = dict(qpos=0.0, qvel=0.0, qacc=0.0, qfrc_actuator=0.0, cfrc_ext=0.0, obs=0.0, reward=0.0, info=0.0,
+             trunk_z=0.0, air_time=0.0)
+    mism = dict(ncon=0, done=0, trunc=0, healthy=0, last_contacts=0, unhealthy_steps=0)
+    for e, t in enumerate(idx):
+        s, d = out["state"][e], out["diag"][e]
+        gold_done = bool(post["terminated"][t] or post["truncated"][t])
+        mism["done"] += int(bool(out["done"][e]) != gold_done)
+        mism["trunc"] += int(bool(out["trunc"][e]) != bool(post["truncated"][t] and not post["terminated"][t]))
+        mism["ncon"] += int(d["ncon"] != int(post["ncon"][t]))
+        mism["healthy"] += int(bool(out["info"][e, 13] > 0.5) != bool(post["healthy"][t]))
+        if not gold_done:
+            w["qpos"] = max(w["qpos"], rel_err(s["qpos"], post["qpos"][t]))
+            w["qvel"] = max(w["qvel"], rel_err(s["qvel"], post["qvel"][t]))
+            w["air_time"] = max(w["air_time"], rel_err(s["feet_air_time"], post["ep_feet_air_time"][t]))
+            mism["last_contacts"] += int(np.any(np.asarray(s["last_contacts"]) != (post["ep_last_contacts"][t] > 0)))
+            mism["unhealthy_steps"] += int(s["unhealthy_steps"] != int(round(float(post["ep_time_unhealthy"][t]) / 0.02)))
+            w["obs"] = max(w["obs"], float(np.abs(out["obs"][e] - post["obs"][t]).max()))
+        else:
+            w["obs"] = max(w["obs"], float(np.abs(out["tobs"][e] - post["obs"][t]).max()))
+        w["qacc"] = max(w["qacc"], rel_err(d["qacc"], post["qacc"][t]))
+        w["qfrc_actuator"] = max(w["qfrc_actuator"], rel_err(d["qfrc_actuator"], post["qfrc_actuator"][t]))
+        w["cfrc_ext"] = max(w["cfrc_ext"], rel_err(d["cfrc_ext"], post["cfrc_ext"][t]))
+        w["trunk_z"] = max(w["trunk_z"], abs(d["trunk_xpos_z"] - post["trunk_z"][t]))
+        w["reward"] = max(w["reward"], abs(float(out["rew"][e]) - float(post["reward"][t])))
+        w["info"] = max(w["info"], float(np.abs(out["info"][e, 2:10] - post["info"][t]).max() /
+                                         max(1.0, np.abs(post["info"][t]).max())))
+    return w, mism
+
+
+def contact_sets_equal(contacts, post, t, tie_eps=1e-6, margin=0.001):
+    """Contact-set equality (robot geom ids with multiplicity) excluding contacts within tie_eps of the margin."""
+    gold = [(int(g), float(dd)) for g, dd in zip(post["con_geom"][t], post["con_dist"][t]) if g >= 0]
+    ours = [(c["geom"], c["dist"]) for c in contacts]
+    near = lambda dd: abs(dd - margin) < tie_eps
+    a = sorted(g for g, dd in gold if not near(dd))
+    b = sorted(g for g, dd in ours if not near(dd))
+    excluded = sum(near(dd) for _, dd in gold) + sum(near(dd) for _, dd in ours)
+    return a == b, excluded

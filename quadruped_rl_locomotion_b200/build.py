@@ -11,7 +11,7 @@ import sys
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 SRC = os.path.join(HERE, "csrc", "go1sim.cu")
-DEPS = [SRC, os.path.join(HERE, "csrc", "go1_physics.cuh"), os.path.join(HERE, "csrc", "go1_model.h"),
+DEPS = [SRC, os.path.join(HERE, "csrc", "go1_warp.cuh"), os.path.join(HERE, "csrc", "go1_model.h"),
         os.path.join(os.path.dirname(HERE), "include", "go1sim.h")]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-Xcompiler", "-fPIC",
               "-shared", "--expt-relaxed-constexpr"]
@@ -32,7 +32,7 @@ def build(force: bool = False, verbose: bool = False, variants=("f32", "f64")) -
         outs[v] = out
         if not force and not _stale(out):
             continue
-        cmd = [nvcc] + NVCC_FLAGS + (["-DGO1_REAL=double", "-DGO1_MINBLOCKS=3"] if v == "f64" else []) + \
+        cmd = [nvcc] + NVCC_FLAGS + (["-DGO1_REAL=double", "-DGO1_MINBLOCKS=1"] if v == "f64" else []) + \
               (["-Xptxas", "-v"] if verbose else []) + ["-o", out, SRC]
         print("[build]", " ".join(cmd), file=sys.stderr)
         subprocess.check_call(cmd)

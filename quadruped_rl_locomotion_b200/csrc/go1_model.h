@@ -17,6 +17,10 @@ constexpr int NLEG = 4;       // lanes per environment: one lane per leg
 constexpr int GMAX = 12;      // collision geoms handled by one lane (its leg's + a share of the trunk's)
 constexpr int CMAX = 16;      // active contacts kept per lane
 constexpr int NCLS = 4;       // distinct floor-contact parameter classes
+constexpr int GFLAT = 44;     // robot collision geoms (flat list, sorted by body)
+
+// index tables of the block-arrow layout tt[21] | tk[4][6][3] | kk[4][6]  (go1_warp.cuh)
+struct ArrowTab { unsigned char sym_r[21], sym_c[21], pad[2]; unsigned char ent_u[120], ent_c[120]; };
 
 enum { G_SPHERE = 2, G_CAPSULE = 3, G_CYLINDER = 5, G_BOX = 6 };
 
@@ -57,6 +61,11 @@ struct DevModel {
     int gstart[NLEG][5];
     DevGeom<T> geoms[NLEG][GMAX];
     DevClass<T> cls[NCLS];
+    // flat geom list sorted by body (slot = body index: 0 trunk, 1 + 3*leg + link) + bounding radii
+    int nflat, pad1;
+    DevGeom<T> flat[GFLAT];
+    T flat_rb[GFLAT];
+    ArrowTab tab;
     // env constants
     T key_qpos[19], key_ctrl[12], soft_lo[12], soft_hi[12], ctrl_lo[12], ctrl_hi[12];
 };
@@ -340,6 +349,45 @@ inline bool build_dev_model(const void* data, size_t nbytes, DevModel<double>& M
         dg.cls = ci;
         tmp[lane][slot].push_back(dg);
     }
+    // flat list in body order: trunk geoms (kept in geom-id order), then every leg body
+    {
+        std::vector<DevGeom<double>> trunk;
+        for (int k = 0; k < NLEG; k++) for (auto& dg : tmp[k][0]) trunk.push_back(dg);
+        for (size_t a = 0; a < trunk.size(); a++)
+            for (size_t b2 = a + 1; b2 < trunk.size(); b2++)
+                if (trunk[b2].gid < trunk[a].gid) std::swap(trunk[a], trunk[b2]);
+        int n = 0;
+        auto push = [&](DevGeom<double> dg, int body) -> bool {
+            if (n >= GFLAT) return false;
+            dg.slot = body;
+            double rb = 0;
+            if (dg.type == G_SPHERE) rb = dg.size[0];
+            else if (dg.type == G_CAPSULE) rb = dg.size[0] + dg.size[1];
+            else if (dg.type == G_CYLINDER) rb = std::sqrt(dg.size[0] * dg.size[0] + dg.size[1] * dg.size[1]);
+            else rb = std::sqrt(dg.size[0] * dg.size[0] + dg.size[1] * dg.size[1] + dg.size[2] * dg.size[2]);
+            M.flat_rb[n] = rb * (1 + 1e-6) + 1e-9;
+            M.flat[n++] = dg;
+            return true;
+        };
+        for (auto& dg : trunk) GO1_REQ(push(dg, 0), "too many collision geoms");
+        for (int k = 0; k < NLEG; k++)
+            for (int s = 1; s < 4; s++)
+                for (auto& dg : tmp[k][s]) GO1_REQ(push(dg, 1 + 3 * k + (s - 1)), "too many collision geoms");
+        M.nflat = n;
+    }
+    // block-arrow index tables
+    {
+        ArrowTab& t = M.tab;
+        std::memset(&t, 0, sizeof(t));
+        for (int r = 0; r < 6; r++)
+            for (int c = 0; c <= r; c++) { int e = r * (r + 1) / 2 + c; t.sym_r[e] = r; t.sym_c[e] = c; t.ent_u[e] = r; t.ent_c[e] = c; }
+        for (int k = 0; k < NLEG; k++) {
+            for (int j = 0; j < 6; j++)
+                for (int i = 0; i < 3; i++) { int e = 21 + 18 * k + 3 * j + i; t.ent_u[e] = 6 + 3 * k + i; t.ent_c[e] = j; }
+            for (int i = 0; i < 3; i++)
+                for (int c = 0; c <= i; c++) { int e = 93 + 6 * k + i * (i + 1) / 2 + c; t.ent_u[e] = 6 + 3 * k + i; t.ent_c[e] = 6 + 3 * k + c; }
+        }
+    }
     for (int k = 0; k < NLEG; k++) {
         int n = 0;
         for (int s = 0; s < 4; s++) {
@@ -372,6 +420,13 @@ inline void cast_dev_model(const DevModel<double>& S, DevModel<T>& D) {
             d.type = s.type; d.slot = s.slot; d.cls = s.cls; d.gid = s.gid;
             for (int c = 0; c < 3; c++) { d.pos[c] = (T)s.pos[c]; d.zax[c] = (T)s.zax[c]; d.xax[c] = (T)s.xax[c]; d.size[c] = (T)s.size[c]; }
         }
+    D.nflat = S.nflat;
+    CPA(flat_rb); CPI(tab);
+    for (int g = 0; g < GFLAT; g++) {
+        const DevGeom<double>& s = S.flat[g]; DevGeom<T>& d = D.flat[g];
+        d.type = s.type; d.slot = s.slot; d.cls = s.cls; d.gid = s.gid;
+        for (int c = 0; c < 3; c++) { d.pos[c] = (T)s.pos[c]; d.zax[c] = (T)s.zax[c]; d.xax[c] = (T)s.xax[c]; d.size[c] = (T)s.size[c]; }
+    }
     for (int c = 0; c < NCLS; c++) {
         const DevClass<double>& s = S.cls[c]; DevClass<T>& d = D.cls[c];
         d.dim = s.dim; d.mu = (T)s.mu; d.K = (T)s.K; d.B = (T)s.B; d.d0 = (T)s.d0; d.d1 = (T)s.d1; d.width = (T)s.width;

@@ -17,6 +17,10 @@ NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", 
               "-shared", "--expt-relaxed-constexpr"]
 
 
+# fp32 product build: MUFU-based division / square root (<= 2 ulp) instead of the IEEE slow paths
+F32_FLAGS = ["-prec-div=false", "-prec-sqrt=false"]
+
+
 def _stale(out: str) -> bool:
     if not os.path.exists(out):
         return True
@@ -32,7 +36,7 @@ def build(force: bool = False, verbose: bool = False, variants=("f32", "f64")) -
         outs[v] = out
         if not force and not _stale(out):
             continue
-        cmd = [nvcc] + NVCC_FLAGS + (["-DGO1_REAL=double", "-DGO1_MINBLOCKS=1"] if v == "f64" else []) + \
+        cmd = [nvcc] + NVCC_FLAGS + (["-DGO1_REAL=double", "-DGO1_MINBLOCKS=1"] if v == "f64" else F32_FLAGS) + \
               (["-Xptxas", "-v"] if verbose else []) + ["-o", out, SRC]
         print("[build]", " ".join(cmd), file=sys.stderr)
         subprocess.check_call(cmd)

@@ -26,6 +26,9 @@ namespace go1 {
 constexpr unsigned FULL = 0xffffffffu;
 constexpr int NB = 13;      // bodies: 0 trunk, 1 + 3*leg + link
 constexpr int NDOF = 18;    // 0..5 trunk (3 lin world, 3 rot body frame), 6 + 3*leg + link
+#ifndef GO1_LS_REL
+#define GO1_LS_REL 1e-2
+#endif
 #ifndef GO1_CW
 #define GO1_CW 48
 #endif
@@ -36,7 +39,7 @@ constexpr int A_TK = 21, A_KK = 93;
 template <typename T> struct Num;
 template <> struct Num<float> {
     static GO1_DEV float sqrt_(float x) { return sqrtf(x); }
-    static GO1_DEV float rsqrt_(float x) { return 1.0f / sqrtf(x); }
+    static GO1_DEV float rsqrt_(float x) { return rsqrtf(x); }
     static GO1_DEV void sincos_(float x, float* s, float* c) { sincosf(x, s, c); }
     static GO1_DEV float pow_(float a, float b) { return powf(a, b); }
     static GO1_DEV float abs_(float a) { return fabsf(a); }
@@ -1202,11 +1205,14 @@ GO1_NOINL void substep_w(const DevModel<T>& m, const EnvCfg<T>& cfg, WEnv<T>& E,
         __syncwarp();
         const T Ms = arrow_matvec(E, E.M, lane);
         body_motion(E, E.xv, E.bv[1], lane);
+#ifdef GO1_EMU_TRACE
+        int g_trace_it = 0;
+#endif
         T alpha = 0;
         {
             const T snorm = N::sqrt_(warp_sum(s * s));
             if (snorm >= N::MINVAL) {
-                const T gtol = tol * m.ls_tolerance * snorm / scale;
+                T gtol = tol * m.ls_tolerance * snorm / scale;
                 ls_prepare(m, E, lane);
                 LSRow<T> lr;
                 lr.fr_jar = a - dr.fr_aref; lr.fr_jv = s;
@@ -1215,8 +1221,17 @@ GO1_NOINL void substep_w(const DevModel<T>& m, const EnvCfg<T>& cfg, WEnv<T>& E,
                 const T g2 = warp_sum(lane < NDOF ? T(0.5) * s * Ms : T(0));
                 const int lsmax = m.ls_iterations;
                 int it = 0;
+#ifdef GO1_EMU_TRACE
+#define GO1_TRACE_IT g_trace_it = it
+#else
+#define GO1_TRACE_IT
+#endif
                 LSPoint<T> p0, p1, p2, pmid, p1n, p2n;
                 p0 = ls_eval(m, E, lane, T(0), g1, g2, dr, lr); it++;
+                // fp32: MuJoCo's absolute tolerance (1e-10 * |search|) is below the rounding noise of d1, the search would
+                // run to the iteration cap; stop when the directional derivative has dropped by GO1_LS_REL instead.  The
+                // Newton exit tests (gradient / decrement) are unchanged, so the optimum is the same.
+                if (sizeof(T) == 4) gtol = N::max_(gtol, T(GO1_LS_REL) * N::abs_(p0.d1));
                 p1 = ls_eval(m, E, lane, p0.alpha - p0.d1 / p0.d2, g1, g2, dr, lr); it++;
                 if (p0.cost < p1.cost) p1 = p0;
                 bool done = false;
@@ -1266,8 +1281,12 @@ GO1_NOINL void substep_w(const DevModel<T>& m, const EnvCfg<T>& cfg, WEnv<T>& E,
                         }
                     }
                 }
+                GO1_TRACE_IT;
             }
         }
+#ifdef GO1_EMU_TRACE
+        if (lane == 0) std::printf("TRACE iter %d ncon %d lsevals %d alpha %.6g cost %.9g impr %.3g grad %.3g\n", iter, ncon, g_trace_it, (double)alpha, (double)cost, (double)improvement, (double)gradient);
+#endif
         if (alpha == 0) break;
         a += alpha * s; Ma += alpha * Ms;
         oldcost = cost;

@@ -63,6 +63,7 @@ struct KParams {
     float* obs; float* rew; uint8_t* done; uint8_t* trunc; float* term_obs; float* info;
     T* diag; int* diag_i; T* diag_con;   // nullable
     double* stats;                 // nullable: 8 doubles
+    int* queue;                    // environment queue head (zeroed before every launch)
     unsigned long long seed, env_offset, launch_counter;
 };
 
@@ -186,10 +187,8 @@ GO1_DEV void reset_env(const DevModel<T>& m, const EnvCfg<T>& cfg, WEnv<T>& E, i
 template <typename T>
 __global__ void __launch_bounds__(GO1_WARPS * 32, GO1_MINBLOCKS) k_step(const KParams<T> P) {
     GO1_DYN_SMEM(smem_raw);
-    __shared__ double sstat[8];
     constexpr size_t MODEL_BYTES = (sizeof(DevModel<T>) + 15) & ~size_t(15);
     DevModel<T>& m = *reinterpret_cast<DevModel<T>*>(smem_raw);
-    if (threadIdx.x < 8) sstat[threadIdx.x] = 0;
     {
         const int* src = reinterpret_cast<const int*>(P.model);
         int* dst = reinterpret_cast<int*>(smem_raw);
@@ -197,12 +196,19 @@ __global__ void __launch_bounds__(GO1_WARPS * 32, GO1_MINBLOCKS) k_step(const KP
     }
     __syncthreads();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int env = blockIdx.x * GO1_WARPS + warp;
     WEnv<T>& E = reinterpret_cast<WEnv<T>*>(smem_raw + MODEL_BYTES)[warp];
     const EnvCfg<T>& cfg = P.cfg;
     const int N = P.n_envs;
     typedef Num<T> NN;
-    if (env < N && !(P.reset_only && P.reset_mask && !P.reset_mask[env])) {
+    double st_acc = 0;     // lane i < 8: i-th rollout statistic summed over the environments this warp stepped
+    // persistent warps: every warp pulls the next environment from a global queue until the slab is done
+    for (;;) {
+        __syncwarp();
+        int env = 0;
+        if (lane == 0) env = atomicAdd(P.queue, 1);
+        env = __shfl_sync(FULL, env, 0);
+        if (env >= N) break;
+        if (P.reset_only && P.reset_mask && !P.reset_mask[env]) continue;
         const unsigned long long gid = P.env_offset + (unsigned long long)env;
         T* sr = P.sreal + (size_t)env * S_STRIDE;
         int* si = P.sint + (size_t)env * I_STRIDE;
@@ -405,13 +411,18 @@ __global__ void __launch_bounds__(GO1_WARPS * 32, GO1_MINBLOCKS) k_step(const KP
                     inf[10] = (float)ep_ret; inf[11] = (float)ep_len; inf[12] = (float)reason; inf[13] = ok ? 1.f : 0.f;
                     inf[14] = (float)out.iters_total; inf[15] = (float)out.ncon;
                 }
-                if (P.stats) {
-                    atomicAdd(&sstat[0], (double)reward); atomicAdd(&sstat[7], 1.0);
-                    if (done) { atomicAdd(&sstat[1], 1.0); atomicAdd(&sstat[2], (double)ep_len); atomicAdd(&sstat[3], (double)ep_ret); }
-                    if (terminated) atomicAdd(&sstat[4], 1.0);
-                    if (truncated && !terminated) atomicAdd(&sstat[5], 1.0);
-                    if (nonfinite) atomicAdd(&sstat[6], 1.0);
-                }
+            }
+            {
+                double v = 0;
+                if (lane == 0) v = (double)reward;
+                else if (lane == 1) v = done ? 1.0 : 0.0;
+                else if (lane == 2) v = done ? (double)ep_len : 0.0;
+                else if (lane == 3) v = done ? (double)ep_ret : 0.0;
+                else if (lane == 4) v = terminated ? 1.0 : 0.0;
+                else if (lane == 5) v = (truncated && !terminated) ? 1.0 : 0.0;
+                else if (lane == 6) v = nonfinite ? 1.0 : 0.0;
+                else if (lane == 7) v = 1.0;
+                st_acc += v;
             }
             if (done) {
                 reset_env(m, cfg, E, lane, P.seed, gid);
@@ -421,11 +432,7 @@ __global__ void __launch_bounds__(GO1_WARPS * 32, GO1_MINBLOCKS) k_step(const KP
             store_state();
         }
     }
-    if (P.stats) {
-        // block-level reduction in shared memory, then at most 8 global atomics per block
-        __syncthreads();
-        if (threadIdx.x < 8 && sstat[threadIdx.x] != 0.0) atomicAdd(P.stats + threadIdx.x, sstat[threadIdx.x]);
-    }
+    if (P.stats && lane < 8 && st_acc != 0.0) atomicAdd(P.stats + lane, st_acc);
 }
 
 // 48-64-64-12 tanh MLP + Gaussian sampling + clip: one thread per env (weights in shared memory).
@@ -480,6 +487,8 @@ struct Go1Sim {
     real* diag = nullptr; int* diag_i = nullptr; real* diag_con = nullptr;
     bool diag_enabled = false;
     double* stats = nullptr;
+    int* queue = nullptr;
+    int grid_blocks = 0;
     float *d_act = nullptr, *d_obs = nullptr, *d_rew = nullptr, *d_tobs = nullptr, *d_info = nullptr;
     uint8_t *d_done = nullptr, *d_trunc = nullptr, *d_mask = nullptr;
     float *h_act = nullptr, *h_obs = nullptr, *h_rew = nullptr, *h_tobs = nullptr, *h_info = nullptr;   // pinned staging
@@ -568,7 +577,7 @@ int go1_create(const void* model_blob, size_t nbytes, const Go1EnvConfig* cfg_in
     const size_t N = (size_t)n_envs;
 #define ALLOC(p, bytes) if ((e = cudaMalloc((void**)&(p), (bytes))) != cudaSuccess) return fail("cudaMalloc " #p, e); cudaMemset((p), 0, (bytes))
     ALLOC(h->sreal, sizeof(real) * S_STRIDE * N); ALLOC(h->sint, sizeof(int) * I_STRIDE * N);
-    ALLOC(h->stats, sizeof(double) * 8);
+    ALLOC(h->stats, sizeof(double) * 8); ALLOC(h->queue, sizeof(int) * 4);
     ALLOC(h->d_act, sizeof(float) * 12 * N); ALLOC(h->d_obs, sizeof(float) * 48 * N); ALLOC(h->d_rew, sizeof(float) * N);
     ALLOC(h->d_tobs, sizeof(float) * 48 * N); ALLOC(h->d_info, sizeof(float) * GO1_INFO_DIM * N);
     ALLOC(h->d_done, N); ALLOC(h->d_trunc, N); ALLOC(h->d_mask, N);
@@ -584,6 +593,17 @@ int go1_create(const void* model_blob, size_t nbytes, const Go1EnvConfig* cfg_in
     cudaMemcpy(h->d_lo, lo, sizeof(lo), cudaMemcpyHostToDevice); cudaMemcpy(h->d_hi, hi, sizeof(hi), cudaMemcpyHostToDevice);
     if ((e = cudaFuncSetAttribute(k_step<real>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)step_smem_bytes())) != cudaSuccess)
         return fail("cudaFuncSetAttribute", e);
+#ifdef GO1_EMU
+    h->grid_blocks = 64;
+#else
+    {
+        int per_sm = 0, sms = 0;
+        if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_step<real>, GO1_WARPS * 32, step_smem_bytes())) != cudaSuccess) return fail("occupancy query", e);
+        if ((e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, cuda_device)) != cudaSuccess) return fail("device attribute", e);
+        if (per_sm < 1) { g_create_err = "k_step does not fit on an SM"; go1_destroy(h); return GO1_ECUDA; }
+        h->grid_blocks = per_sm * sms;      // persistent warps: one resident wave
+    }
+#endif
     *out = h;
     int rc = go1_reset(h, nullptr, nullptr, nullptr);
     if (rc != GO1_OK) { g_create_err = h->err; go1_destroy(h); *out = nullptr; return rc; }
@@ -595,7 +615,7 @@ int go1_destroy(go1_handle h) {
     if (!h) return GO1_EINVAL;
     cudaSetDevice(h->device);
     if (h->stream) cudaStreamSynchronize(h->stream);
-    void* dev[] = {h->dmodel, h->sreal, h->sint, h->diag, h->diag_i, h->diag_con, h->stats, h->d_act, h->d_obs, h->d_rew, h->d_tobs,
+    void* dev[] = {h->queue, h->dmodel, h->sreal, h->sint, h->diag, h->diag_i, h->diag_con, h->stats, h->d_act, h->d_obs, h->d_rew, h->d_tobs,
                    h->d_info, h->d_done, h->d_trunc, h->d_mask, h->d_lo, h->d_hi};
     for (void* p : dev) if (p) cudaFree(p);
     void* host[] = {h->h_act, h->h_obs, h->h_rew, h->h_tobs, h->h_info, h->h_done, h->h_trunc, h->h_mask};
@@ -619,12 +639,14 @@ static KParams<real> base_params(go1_handle h) {
     KParams<real> P;
     std::memset(&P, 0, sizeof(P));
     P.model = h->dmodel; P.cfg = h->cfg; P.n_envs = h->n_envs; P.sreal = h->sreal; P.sint = h->sint;
-    P.seed = h->seed; P.env_offset = h->env_offset; P.launch_counter = h->launch_counter;
+    P.seed = h->seed; P.env_offset = h->env_offset; P.launch_counter = h->launch_counter; P.queue = h->queue;
     if (h->diag_enabled) { P.diag = h->diag; P.diag_i = h->diag_i; P.diag_con = h->diag_con; }
     return P;
 }
 static int launch(go1_handle h, const KParams<real>& P, cudaStream_t s) {
-    const int grid = (h->n_envs + GO1_WARPS - 1) / GO1_WARPS;
+    int grid = (h->n_envs + GO1_WARPS - 1) / GO1_WARPS;
+    if (grid > h->grid_blocks) grid = h->grid_blocks;
+    CK(cudaMemsetAsync(h->queue, 0, sizeof(int), s));
     GO1_LAUNCH(k_step<real>, grid, GO1_WARPS * 32, step_smem_bytes(), s, P);
     CK(cudaGetLastError());
     return GO1_OK;

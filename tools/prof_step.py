@@ -19,7 +19,8 @@ def main():
     warm = int(sys.argv[2]) if len(sys.argv) > 2 else 20
     steps = int(sys.argv[3]) if len(sys.argv) > 3 else 5
     ctrl = sys.argv[4] if len(sys.argv) > 4 else "torque"
-    sim = Sim(load_model_blob(ctrl), n, lib=Go1Lib(), seed=1234)
+    libpath = os.environ.get("GO1_LIB")          # alternative build of the same source (tuning experiments)
+    sim = Sim(load_model_blob(ctrl), n, lib=Go1Lib(libpath) if libpath else Go1Lib(), seed=1234)
     for _ in range(warm):
         sim.rollout(1, ACTION_RANDOM, None)
     tot = 0.0

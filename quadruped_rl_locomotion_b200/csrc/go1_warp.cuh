@@ -29,6 +29,9 @@ constexpr int NDOF = 18;    // 0..5 trunk (3 lin world, 3 rot body frame), 6 + 3
 #ifndef GO1_LS_REL
 #define GO1_LS_REL 1e-2
 #endif
+#ifndef GO1_LOCKSTEP
+#define GO1_LOCKSTEP 1
+#endif
 #ifndef GO1_CW
 #define GO1_CW 48
 #endif
@@ -871,11 +874,19 @@ template <typename T> GO1_DEV void store_inert21(T* K, const T* i) {
 // one physics substep (mj_step) of the environment owned by this warp
 template <typename T>
 GO1_NOINL void substep_w(const DevModel<T>& m, const EnvCfg<T>& cfg, WEnv<T>& E, const int lane, SubOut<T>& out,
-                         const bool capture, T* con_out) {
+                         const bool capture, T* con_out, const bool active) {
     typedef Num<T> N;
     const T h = m.timestep;
     const int jl = lane >= 6 && lane < NDOF ? lane - 6 : 0;      // leg-dof index of this lane (0..11)
     const bool legdof = lane >= 6 && lane < NDOF;
+    T qfa = 0, qfs = 0, as_ = 0;
+    DofRows<T> dr;
+    dr.fr_aref = 0; dr.lim_s = 0; dr.lim_D = 0; dr.lim_aref = 0; dr.floss = 0; dr.Rf = 1;
+    int ncon = 0;
+#if GO1_LOCKSTEP
+    __syncthreads();     // the warps of a block run the substep phases together: they share instruction fetches
+#endif
+    if (active) {
     // ------------------------------------------------------------------ mj_kinematics
     T R0[9];
     {
@@ -1017,7 +1028,7 @@ GO1_NOINL void substep_w(const DevModel<T>& m, const EnvCfg<T>& cfg, WEnv<T>& E,
         }
         __syncwarp();
     }
-    const int ncon = E.ncon;
+    ncon = E.ncon;
     // ------------------------------------------------------------------ mj_crb -> block-arrow M (+ armature)
     composite21(E.crb, (const T (*)[21]) nullptr, lane);
     assemble_arrow(m, E, E.crb, E.M, lane);
@@ -1058,9 +1069,7 @@ GO1_NOINL void substep_w(const DevModel<T>& m, const EnvCfg<T>& cfg, WEnv<T>& E,
         __syncwarp();
         bias = force_to_joint(E, E.bv[2], lane);
     }
-    T qfa = 0, qfs = -bias;
-    DofRows<T> dr;
-    dr.fr_aref = 0; dr.lim_s = 0; dr.lim_D = 0; dr.lim_aref = 0; dr.floss = 0; dr.Rf = 1;
+    qfs = -bias;
     if (legdof) {
         const T ql = E.qpos[7 + jl], vl = E.qvel[6 + jl];
         T u = E.ctrl[jl];
@@ -1094,7 +1103,7 @@ GO1_NOINL void substep_w(const DevModel<T>& m, const EnvCfg<T>& cfg, WEnv<T>& E,
     for (int idx = lane; idx < NARROW; idx += 32) E.H[idx] = E.M[idx];
     __syncwarp();
     arrow_factor(m, E.H, lane);
-    const T as_ = arrow_solve(E, E.H, qfs, lane);
+    as_ = arrow_solve(E, E.H, qfs, lane);
     // ------------------------------------------------------------------ contact rows: impedance, D, reference acceleration
     {
         const T* F = m.plane_frame;
@@ -1131,6 +1140,7 @@ GO1_NOINL void substep_w(const DevModel<T>& m, const EnvCfg<T>& cfg, WEnv<T>& E,
         if (capture && lane == 0) con_out[0] = (T)ncon;
     }
     __syncwarp();
+    }   // active
     // ------------------------------------------------------------------ mj_fwdConstraint: warmstart + Newton
     T a = as_, Ma = qfs, qfc = 0, hdiag = 0, grad = 0, cost = 0, oldcost = 0;
     const T scale = T(1) / (m.meaninertia * T(18));
@@ -1140,8 +1150,16 @@ GO1_NOINL void substep_w(const DevModel<T>& m, const EnvCfg<T>& cfg, WEnv<T>& E,
     T cost_s = 0, improvement = 0, gradient = 0;
     bool first = true;
     T* frc_out = capture ? con_out : (T*)nullptr;
+    bool conv = !active;
 #pragma unroll 1
     while (true) {
+#if GO1_LOCKSTEP
+        if (__syncthreads_and(conv)) break;       // one Newton round per barrier, until every warp of the block converged
+#else
+        if (conv) break;
+#endif
+        if (conv) continue;
+        do {
         if (lane < NDOF) E.xv[lane] = a;
         __syncwarp();
         body_motion(E, E.xv, E.bv[0], lane);
@@ -1155,7 +1173,7 @@ GO1_NOINL void substep_w(const DevModel<T>& m, const EnvCfg<T>& cfg, WEnv<T>& E,
             __syncwarp();
             Ma = arrow_matvec(E, E.M, lane);
             __syncwarp();
-            continue;
+            break;
         }
         if (phase == 1) {
             phase = 2;
@@ -1165,7 +1183,7 @@ GO1_NOINL void substep_w(const DevModel<T>& m, const EnvCfg<T>& cfg, WEnv<T>& E,
                 __syncwarp();
                 Ma = arrow_matvec(E, E.M, lane);
                 __syncwarp();
-                continue;
+                break;
             }
         }
         grad = lane < NDOF ? Ma - qfs - qfc : T(0);
@@ -1176,12 +1194,12 @@ GO1_NOINL void substep_w(const DevModel<T>& m, const EnvCfg<T>& cfg, WEnv<T>& E,
         }
         first = false;
         cost = cnew;
-        if (iter >= maxiter) break;
+        if (iter >= maxiter) { conv = true; break; }
         // MuJoCo's exit test (after >= 1 move): gradient small, or improvement small.  The measured improvement is a
         // difference of O(cost) numbers and is pure rounding noise in fp32 once it drops below ~1e-7*cost, so
         // "improvement small" is only trusted when the Newton decrement -g.s/2 (the predicted improvement of the
         // next move, free of cancellation) is small too; see DESIGN.md.
-        if (iter > 0 && gradient < tol) break;
+        if (iter > 0 && gradient < tol) { conv = true; break; }
         // ---- Hessian H = M + J'DJ (+ cone blocks), block-arrow; search = -H^-1 grad
         if (contact_stiffness(m, E, lane)) {
             composite21(E.Kc, E.crb, lane);
@@ -1198,7 +1216,7 @@ GO1_NOINL void substep_w(const DevModel<T>& m, const EnvCfg<T>& cfg, WEnv<T>& E,
         const T s = -arrow_solve(E, E.H, grad, lane);
         if (iter > 0 && improvement < tol) {
             const T dec = warp_sum(grad * s);
-            if (T(-0.5) * scale * dec < tol) break;
+            if (T(-0.5) * scale * dec < tol) { conv = true; break; }
         }
         // ---- exact line search (PrimalSearch)
         if (lane < NDOF) E.xv[lane] = s;
@@ -1287,10 +1305,12 @@ GO1_NOINL void substep_w(const DevModel<T>& m, const EnvCfg<T>& cfg, WEnv<T>& E,
 #ifdef GO1_EMU_TRACE
         if (lane == 0) std::printf("TRACE iter %d ncon %d lsevals %d alpha %.6g cost %.9g impr %.3g grad %.3g\n", iter, ncon, g_trace_it, (double)alpha, (double)cost, (double)improvement, (double)gradient);
 #endif
-        if (alpha == 0) break;
+        if (alpha == 0) { conv = true; break; }
         a += alpha * s; Ma += alpha * Ms;
         oldcost = cost;
+        } while (0);
     }
+    if (!active) return;
     out.iters = iter; out.iters_total += iter;
     out.ncon = ncon;
     out.overflow += E.overflow;

@@ -28,10 +28,10 @@
 #define GO1_REAL float
 #endif
 #ifndef GO1_WARPS
-#define GO1_WARPS 4          // environments (warps) per block
+#define GO1_WARPS 8          // environments (warps) per block
 #endif
 #ifndef GO1_MINBLOCKS
-#define GO1_MINBLOCKS 4
+#define GO1_MINBLOCKS 2
 #endif
 
 namespace go1 {
@@ -201,14 +201,22 @@ __global__ void __launch_bounds__(GO1_WARPS * 32, GO1_MINBLOCKS) k_step(const KP
     const int N = P.n_envs;
     typedef Num<T> NN;
     double st_acc = 0;     // lane i < 8: i-th rollout statistic summed over the environments this warp stepped
-    // persistent warps: every warp pulls the next environment from a global queue until the slab is done
+    // persistent blocks: the block pulls the next GO1_WARPS environments from a global queue until the slab is done
+    __shared__ int s_base;
     for (;;) {
-        __syncwarp();
-        int env = 0;
-        if (lane == 0) env = atomicAdd(P.queue, 1);
-        env = __shfl_sync(FULL, env, 0);
-        if (env >= N) break;
-        if (P.reset_only && P.reset_mask && !P.reset_mask[env]) continue;
+        __syncthreads();
+        if (threadIdx.x == 0) s_base = atomicAdd(P.queue, GO1_WARPS);
+        __syncthreads();
+        const int env = s_base + warp;
+        if (s_base >= N) break;
+        const bool active = env < N && !(P.reset_only && P.reset_mask && !P.reset_mask[env]);
+        if (P.reset_only && !active) continue;
+        if (!active) {      // keeps the block's barriers balanced
+            SubOut<T> dummy;
+            dummy.iters_total = 0; dummy.overflow = 0; dummy.bad = 0;
+            for (int s = 0; s < cfg.frame_skip; s++) substep_w(m, cfg, E, lane, dummy, false, (T*)nullptr, false);
+            continue;
+        }
         const unsigned long long gid = P.env_offset + (unsigned long long)env;
         T* sr = P.sreal + (size_t)env * S_STRIDE;
         int* si = P.sint + (size_t)env * I_STRIDE;
@@ -262,9 +270,9 @@ __global__ void __launch_bounds__(GO1_WARPS * 32, GO1_MINBLOCKS) k_step(const KP
                 if (lane == 0) { E.ncon = 0; E.overflow = 0; }
                 __syncwarp();
             }
-            for (int s = 0; s < cfg.frame_skip && !out.bad; s++) {
+            for (int s = 0; s < cfg.frame_skip; s++) {
                 const bool last = s == cfg.frame_skip - 1;
-                substep_w(m, cfg, E, lane, out, capture && last, con_out);
+                substep_w(m, cfg, E, lane, out, capture && last, con_out, !out.bad);
             }
             if (out.bad) { out.qacc = 0; out.qfa = 0; out.qfc = 0; out.trunk_z = 0; }
             const bool legdof = lane >= 6 && lane < NDOF;

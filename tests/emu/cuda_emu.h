@@ -171,6 +171,8 @@ inline int __all_sync(unsigned m, int pred) {
     return (__ballot_sync(m, pred) & livemask) == livemask;
 }
 inline void __syncthreads() { emu_barrier(); }
+inline int __syncthreads_and(int pred) { return __all_sync(0xffffffffu, pred); }   // a block is one warp here
+inline int __syncthreads_or(int pred) { return __any_sync(0xffffffffu, pred); }
 inline void __syncwarp(unsigned = 0xffffffffu) { emu_barrier(); }
 inline unsigned __umulhi(unsigned a, unsigned b) { return (unsigned)(((unsigned long long)a * b) >> 32); }
 inline int __popc(unsigned v) { return __builtin_popcount(v); }

@@ -20,7 +20,8 @@ constexpr int NCLS = 4;       // distinct floor-contact parameter classes
 constexpr int GFLAT = 44;     // robot collision geoms (flat list, sorted by body)
 
 // index tables of the block-arrow layout tt[21] | tk[4][6][3] | kk[4][6]  (go1_warp.cuh)
-struct ArrowTab { unsigned char sym_r[21], sym_c[21], pad[2]; unsigned char ent_u[120], ent_c[120]; };
+// crb_idx / crb_sgn: entry e of the packed 6x6 spatial inertia = crb_sgn[e] * cinert[crb_idx[e]] (mju_mulInertVec)
+struct ArrowTab { unsigned char sym_r[21], sym_c[21], pad[2]; unsigned char ent_u[120], ent_c[120]; signed char crb_idx[24], crb_sgn[24]; };
 
 enum { G_SPHERE = 2, G_CAPSULE = 3, G_CYLINDER = 5, G_BOX = 6 };
 
@@ -57,9 +58,6 @@ struct DevModel {
     int act_id[NLEG][3], act_climited[NLEG][3], act_flimited[NLEG][3], act_bias[NLEG][3];
     T act_gear[NLEG][3], act_gain[NLEG][3], act_b0[NLEG][3], act_b1[NLEG][3], act_b2[NLEG][3];
     T act_clo[NLEG][3], act_chi[NLEG][3], act_flo[NLEG][3], act_fhi[NLEG][3];
-    // geoms per lane, grouped by slot
-    int gstart[NLEG][5];
-    DevGeom<T> geoms[NLEG][GMAX];
     DevClass<T> cls[NCLS];
     // flat geom list sorted by body (slot = body index: 0 trunk, 1 + 3*leg + link) + bounding radii
     int nflat, pad1;
@@ -379,6 +377,9 @@ inline bool build_dev_model(const void* data, size_t nbytes, DevModel<double>& M
     {
         ArrowTab& t = M.tab;
         std::memset(&t, 0, sizeof(t));
+        const int ci[21] = {0, 3, 1, 4, 5, 2, 0, 8, 7, 9, 8, 0, 6, 0, 9, 7, 6, 0, 0, 0, 9};
+        const int cs[21] = {1, 1, 1, 1, 1, 1, 0, 1, -1, 1, -1, 0, 1, 0, 1, 1, -1, 0, 0, 0, 1};
+        for (int e = 0; e < 21; e++) { t.crb_idx[e] = (signed char)ci[e]; t.crb_sgn[e] = (signed char)cs[e]; }
         for (int r = 0; r < 6; r++)
             for (int c = 0; c <= r; c++) { int e = r * (r + 1) / 2 + c; t.sym_r[e] = r; t.sym_c[e] = c; t.ent_u[e] = r; t.ent_c[e] = c; }
         for (int k = 0; k < NLEG; k++) {
@@ -387,14 +388,6 @@ inline bool build_dev_model(const void* data, size_t nbytes, DevModel<double>& M
             for (int i = 0; i < 3; i++)
                 for (int c = 0; c <= i; c++) { int e = 93 + 6 * k + i * (i + 1) / 2 + c; t.ent_u[e] = 6 + 3 * k + i; t.ent_c[e] = 6 + 3 * k + c; }
         }
-    }
-    for (int k = 0; k < NLEG; k++) {
-        int n = 0;
-        for (int s = 0; s < 4; s++) {
-            M.gstart[k][s] = n;
-            for (auto& dg : tmp[k][s]) { GO1_REQ(n < GMAX, "too many collision geoms for one lane"); M.geoms[k][n++] = dg; }
-        }
-        M.gstart[k][4] = n;
     }
     return true;
 }
@@ -413,13 +406,6 @@ inline void cast_dev_model(const DevModel<double>& S, DevModel<T>& D) {
     CPA(floss); CPA(Rf); CPA(Bf); CPA(lim_lo); CPA(lim_hi); CPA(lim_K); CPA(lim_B); CPA(lim_imp); CPA(lim_margin); CPA(dof_invw);
     CPI(limited); CPI(act_id); CPI(act_climited); CPI(act_flimited); CPI(act_bias);
     CPA(act_gear); CPA(act_gain); CPA(act_b0); CPA(act_b1); CPA(act_b2); CPA(act_clo); CPA(act_chi); CPA(act_flo); CPA(act_fhi);
-    CPI(gstart);
-    for (int k = 0; k < NLEG; k++)
-        for (int g = 0; g < GMAX; g++) {
-            const DevGeom<double>& s = S.geoms[k][g]; DevGeom<T>& d = D.geoms[k][g];
-            d.type = s.type; d.slot = s.slot; d.cls = s.cls; d.gid = s.gid;
-            for (int c = 0; c < 3; c++) { d.pos[c] = (T)s.pos[c]; d.zax[c] = (T)s.zax[c]; d.xax[c] = (T)s.xax[c]; d.size[c] = (T)s.size[c]; }
-        }
     D.nflat = S.nflat;
     CPA(flat_rb); CPI(tab);
     for (int g = 0; g < GFLAT; g++) {

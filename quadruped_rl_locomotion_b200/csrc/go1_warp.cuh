@@ -33,7 +33,7 @@ constexpr int NDOF = 18;    // 0..5 trunk (3 lin world, 3 rot body frame), 6 + 3
 #define GO1_LOCKSTEP 1
 #endif
 #ifndef GO1_CW
-#define GO1_CW 48
+#define GO1_CW 40
 #endif
 constexpr int CW = GO1_CW;  // contacts kept per environment (geom order; the rest is counted as overflow)
 constexpr int NARROW = 117; // block-arrow storage: tt[21] | tk[4][6][3] | kk[4][6]
@@ -158,15 +158,14 @@ template <typename T> struct WEnv {
     T qpos[19], qvel[18], warm[18], last_act[12], air[4], dev[3], vdes[3], ep_ret, pad_[2];
     T ctrl[12];
     int ei[8];                       // step, unhealthy_steps, last_contacts, reset_count, bad_state
-    T xmat[NB][9], xpos[NB][3];      // body frames, positions relative to the trunk origin (world axes)
     T com[4];                        // robot COM relative to the trunk origin
     T comw[4];                       // world COM at the start of the last substep (subtree_com)
     T cdof[NDOF][6];                 // motion axes [ang; lin] about the COM
-    T crb[NB][21];                   // composite spatial inertia about the COM, packed symmetric 6x6
-    T Kc[NB][21];                    // per-body contact stiffness -> composite -> + crb
-    T ubuf[NDOF][6];
+    T crb[NB][10];                   // composite spatial inertia about the COM (mju_inertCom layout)
+    T Kc[NB][21];                    // per-body contact stiffness -> composite -> + crb.  During kinematics / collision
+                                     // the same words hold the body frames (xmat 13x9, xpos 13x3; dead before the Newton loop)
     T M[120], H[120];                // block-arrow matrices; H is factored in place
-    T bv[3][NB][6];                  // per-body spatial vectors: 0 = cvel, then A (for qacc); 1 = S (search); 2 = wrenches
+    T bv[2][NB][6];                  // per-body spatial vectors: 0 = cvel, then A (for qacc); 1 = S (search) or body wrenches
     T xv[20];                        // joint-space vector being broadcast
     T cfrc[NB][6];                   // own contact wrench of every body about the COM (cfrc_ext of the last evaluation)
     T c_r[3][CW], c_D0[CW], c_aref[6][CW];
@@ -174,6 +173,11 @@ template <typename T> struct WEnv {
     int c_meta[CW];                  // body | class << 8 | geom id << 16
     int bstart[NB + 3];              // contacts of body b: [bstart[b], bstart[b+1])
     int ncon, overflow;
+    // aliases (lifetimes do not overlap, see DESIGN.md "shared-memory budget")
+    GO1_DEV T (*xmat())[9] { return reinterpret_cast<T (*)[9]>(&Kc[0][0]); }
+    GO1_DEV T (*xpos())[3] { return reinterpret_cast<T (*)[3]>(&Kc[0][0] + NB * 9); }
+    GO1_DEV T (*ubuf())[6] { return reinterpret_cast<T (*)[6]>(&c_s[0][0]); }      // assemble_arrow scratch (c_s is dead then)
+    GO1_DEV T (*wrench())[6] { return bv[1]; }
 };
 
 
@@ -220,22 +224,43 @@ template <typename T> GO1_NOINL T force_to_joint(WEnv<T>& E, T (*W)[6], int lane
     return r;
 }
 
-// composite pass over packed 6x6 matrices: K[b] <- sum of K over the subtree of b, plus base[b] (lanes e < 21)
-template <typename T> GO1_DEV void composite21(T (*K)[21], const T (*base)[21], int lane) {
-    if (lane < 21) {
-        T acc = K[0][lane];
+// composite pass over the 10-parameter spatial inertias (mj_crb accumulation): lanes e < 10
+template <typename T> GO1_DEV void composite10(T (*I)[10], int lane) {
+    if (lane < 10) {
+        T acc = I[0][lane];
 #pragma unroll
         for (int k = 0; k < 4; k++) {
-            const T k3 = K[3 + 3 * k][lane];
-            const T k2 = K[2 + 3 * k][lane] + k3;
-            const T k1 = K[1 + 3 * k][lane] + k2;
+            const T k3 = I[3 + 3 * k][lane];
+            const T k2 = I[2 + 3 * k][lane] + k3;
+            const T k1 = I[1 + 3 * k][lane] + k2;
             acc += k1;
-            if (base) {
-                K[3 + 3 * k][lane] = k3 + base[3 + 3 * k][lane]; K[2 + 3 * k][lane] = k2 + base[2 + 3 * k][lane];
-                K[1 + 3 * k][lane] = k1 + base[1 + 3 * k][lane];
-            } else { K[2 + 3 * k][lane] = k2; K[1 + 3 * k][lane] = k1; }
+            I[2 + 3 * k][lane] = k2; I[1 + 3 * k][lane] = k1;
         }
-        K[0][lane] = base ? acc + base[0][lane] : acc;
+        I[0][lane] = acc;
+    }
+    __syncwarp();
+}
+
+// K[b] <- (sum of K over the subtree of b, if `accumulate`) + the composite inertia crb[b] expanded to a packed 6x6
+// (lanes e < 21; entry e of the 6x6 is sgn * crb[idx], see store order in DevModel::tab)
+template <typename T> GO1_DEV void composite21(const DevModel<T>& m, T (*K)[21], const T (*crb)[10], bool accumulate, int lane) {
+    if (lane < 21) {
+        const int idx = m.tab.crb_idx[lane];
+        const T sg = (T)m.tab.crb_sgn[lane];
+        T acc = accumulate ? K[0][lane] : T(0);
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            T k3 = 0, k2 = 0, k1 = 0;
+            if (accumulate) {
+                k3 = K[3 + 3 * k][lane];
+                k2 = K[2 + 3 * k][lane] + k3;
+                k1 = K[1 + 3 * k][lane] + k2;
+                acc += k1;
+            }
+            K[3 + 3 * k][lane] = k3 + sg * crb[3 + 3 * k][idx]; K[2 + 3 * k][lane] = k2 + sg * crb[2 + 3 * k][idx];
+            K[1 + 3 * k][lane] = k1 + sg * crb[1 + 3 * k][idx];
+        }
+        K[0][lane] = acc + sg * crb[0][idx];
     }
     __syncwarp();
 }
@@ -249,7 +274,7 @@ template <typename T> GO1_NOINL void assemble_arrow(const DevModel<T>& m, WEnv<T
         T s = 0;
 #pragma unroll
         for (int c = 0; c < 6; c++) s += K[b][SYM(r, c)] * E.cdof[d][c];
-        E.ubuf[d][r] = s;
+        E.ubuf()[d][r] = s;
     }
     __syncwarp();
 #pragma unroll 1
@@ -257,7 +282,7 @@ template <typename T> GO1_NOINL void assemble_arrow(const DevModel<T>& m, WEnv<T
         const int u = m.tab.ent_u[idx], c = m.tab.ent_c[idx];
         T s = 0;
 #pragma unroll
-        for (int e = 0; e < 6; e++) s += E.cdof[c][e] * E.ubuf[u][e];
+        for (int e = 0; e < 6; e++) s += E.cdof[c][e] * E.ubuf()[u][e];
         out[idx] = s;
     }
     __syncwarp();
@@ -652,10 +677,10 @@ GO1_DEV T evaluate_rows(const DevModel<T>& m, WEnv<T>& E, int lane, T a, const D
         const int b = idx / 6, e = idx - 6 * b;
         T s = 0;
         for (int c = E.bstart[b]; c < E.bstart[b + 1]; c++) s += E.c_s[e][c];
-        E.bv[2][b][e] = s; E.cfrc[b][e] = s;
+        E.wrench()[b][e] = s; E.cfrc[b][e] = s;
     }
     __syncwarp();
-    qfc = force_to_joint(E, E.bv[2], lane) + fd;
+    qfc = force_to_joint(E, E.wrench(), lane) + fd;
     return cost;
 }
 
@@ -861,13 +886,6 @@ GO1_NOINL LSPoint<T> ls_eval(const DevModel<T>& m, const WEnv<T>& E, int lane, T
 }
 
 
-template <typename T> GO1_DEV void store_inert21(T* K, const T* i) {
-    K[0] = i[0]; K[1] = i[3]; K[2] = i[1]; K[3] = i[4]; K[4] = i[5]; K[5] = i[2];
-    K[6] = 0; K[7] = i[8]; K[8] = -i[7]; K[9] = i[9];
-    K[10] = -i[8]; K[11] = 0; K[12] = i[6]; K[13] = 0; K[14] = i[9];
-    K[15] = i[7]; K[16] = -i[6]; K[17] = 0; K[18] = 0; K[19] = 0; K[20] = i[9];
-}
-
 #define GO1_LEGF(field, j) ((&m.field[0][0])[j])
 
 // ---------------------------------------------------------------------------------------------
@@ -949,12 +967,13 @@ GO1_NOINL void substep_w(const DevModel<T>& m, const EnvCfg<T>& cfg, WEnv<T>& E,
         for (int k = 0; k < 3; k++) com[k] = warp_sum(mass * xip[k]) * inv;
         if (lane < NB) {
 #pragma unroll
-            for (int e = 0; e < 9; e++) E.xmat[mybody][e] = Rb[e];
+            for (int e = 0; e < 9; e++) E.xmat()[mybody][e] = Rb[e];
 #pragma unroll
-            for (int e = 0; e < 3; e++) E.xpos[mybody][e] = pb[e];
+            for (int e = 0; e < 3; e++) E.xpos()[mybody][e] = pb[e];
             const T dif[3] = {xip[0] - com[0], xip[1] - com[1], xip[2] - com[2]};
             cinert_of(cin, Rb, Ib, mass, dif);
-            store_inert21(E.crb[mybody], cin);
+#pragma unroll
+            for (int e = 0; e < 10; e++) E.crb[mybody][e] = cin[e];
         }
         if (lane < 12) {
             const T off[3] = {com[0] - pb[0], com[1] - pb[1], com[2] - pb[2]};
@@ -995,9 +1014,9 @@ GO1_NOINL void substep_w(const DevModel<T>& m, const EnvCfg<T>& cfg, WEnv<T>& E,
                 const int b = g.slot;
                 T Rg[9], gp[3];
 #pragma unroll
-                for (int e = 0; e < 9; e++) Rg[e] = E.xmat[b][e];
+                for (int e = 0; e < 9; e++) Rg[e] = E.xmat()[b][e];
                 matvec3(gp, Rg, g.pos);
-                gp[0] += E.xpos[b][0]; gp[1] += E.xpos[b][1]; gp[2] += E.xpos[b][2];
+                gp[0] += E.xpos()[b][0]; gp[1] += E.xpos()[b][1]; gp[2] += E.xpos()[b][2];
                 const T dc = plane_d0 + dot3(m.plane_frame, gp);
                 meta = b | (g.cls << 8) | (g.gid << 16);
                 if (dc - m.flat_rb[gi] <= m.cls[g.cls].margin) collide_geom(m, g, Rg, gp, dc, st);
@@ -1030,8 +1049,9 @@ GO1_NOINL void substep_w(const DevModel<T>& m, const EnvCfg<T>& cfg, WEnv<T>& E,
     }
     ncon = E.ncon;
     // ------------------------------------------------------------------ mj_crb -> block-arrow M (+ armature)
-    composite21(E.crb, (const T (*)[21]) nullptr, lane);
-    assemble_arrow(m, E, E.crb, E.M, lane);
+    composite10(E.crb, lane);
+    composite21(m, E.Kc, E.crb, false, lane);          // (overwrites xmat / xpos: collision is done)
+    assemble_arrow(m, E, E.Kc, E.M, lane);
     if (legdof) { const int k = jl / 3, i = jl - 3 * k; E.M[A_KK + 6 * k + SYM(i, i)] += GO1_LEGF(armature, jl); }
     __syncwarp();
     // ------------------------------------------------------------------ mj_comVel + mj_rne (bias) + passive + actuation
@@ -1064,10 +1084,10 @@ GO1_NOINL void substep_w(const DevModel<T>& m, const EnvCfg<T>& cfg, WEnv<T>& E,
             mul_inert(t2, cin, cv);
             cross_force(t3, cv, t2);
 #pragma unroll
-            for (int e = 0; e < 6; e++) E.bv[2][mybody][e] = t1[e] + t3[e];
+            for (int e = 0; e < 6; e++) E.wrench()[mybody][e] = t1[e] + t3[e];
         }
         __syncwarp();
-        bias = force_to_joint(E, E.bv[2], lane);
+        bias = force_to_joint(E, E.wrench(), lane);
     }
     qfs = -bias;
     if (legdof) {
@@ -1202,7 +1222,7 @@ GO1_NOINL void substep_w(const DevModel<T>& m, const EnvCfg<T>& cfg, WEnv<T>& E,
         if (iter > 0 && gradient < tol) { conv = true; break; }
         // ---- Hessian H = M + J'DJ (+ cone blocks), block-arrow; search = -H^-1 grad
         if (contact_stiffness(m, E, lane)) {
-            composite21(E.Kc, E.crb, lane);
+            composite21(m, E.Kc, E.crb, true, lane);
             assemble_arrow(m, E, E.Kc, E.H, lane);
             if (legdof) { const int k = jl / 3, i = jl - 3 * k; E.H[A_KK + 6 * k + SYM(i, i)] += GO1_LEGF(armature, jl) + hdiag; }
         } else {

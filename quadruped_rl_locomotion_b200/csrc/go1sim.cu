@@ -28,7 +28,7 @@
 #define GO1_REAL float
 #endif
 #ifndef GO1_WARPS
-#define GO1_WARPS 8          // environments (warps) per block
+#define GO1_WARPS 12         // environments (warps) per block
 #endif
 #ifndef GO1_MINBLOCKS
 #define GO1_MINBLOCKS 2

@@ -32,6 +32,9 @@ constexpr int NDOF = 18;    // 0..5 trunk (3 lin world, 3 rot body frame), 6 + 3
 #ifndef GO1_LOCKSTEP
 #define GO1_LOCKSTEP 1
 #endif
+#ifndef GO1_LS_FAST_MAX
+#define GO1_LS_FAST_MAX 10
+#endif
 #ifndef GO1_CW
 #define GO1_CW 40
 #endif
@@ -1214,12 +1217,16 @@ GO1_NOINL void substep_w(const DevModel<T>& m, const EnvCfg<T>& cfg, WEnv<T>& E,
         }
         first = false;
         cost = cnew;
+#ifdef GO1_DBG_FIXED_ITERS
+        if (iter >= GO1_DBG_FIXED_ITERS) { conv = true; break; }      // timing experiment only: same trip count everywhere
+#else
         if (iter >= maxiter) { conv = true; break; }
         // MuJoCo's exit test (after >= 1 move): gradient small, or improvement small.  The measured improvement is a
         // difference of O(cost) numbers and is pure rounding noise in fp32 once it drops below ~1e-7*cost, so
         // "improvement small" is only trusted when the Newton decrement -g.s/2 (the predicted improvement of the
         // next move, free of cancellation) is small too; see DESIGN.md.
         if (iter > 0 && gradient < tol) { conv = true; break; }
+#endif
         // ---- Hessian H = M + J'DJ (+ cone blocks), block-arrow; search = -H^-1 grad
         if (contact_stiffness(m, E, lane)) {
             composite21(m, E.Kc, E.crb, true, lane);
@@ -1236,7 +1243,9 @@ GO1_NOINL void substep_w(const DevModel<T>& m, const EnvCfg<T>& cfg, WEnv<T>& E,
         const T s = -arrow_solve(E, E.H, grad, lane);
         if (iter > 0 && improvement < tol) {
             const T dec = warp_sum(grad * s);
+#ifndef GO1_DBG_FIXED_ITERS
             if (T(-0.5) * scale * dec < tol) { conv = true; break; }
+#endif
         }
         // ---- exact line search (PrimalSearch)
         if (lane < NDOF) E.xv[lane] = s;
@@ -1257,13 +1266,60 @@ GO1_NOINL void substep_w(const DevModel<T>& m, const EnvCfg<T>& cfg, WEnv<T>& E,
                 lr.lim_jar = dr.lim_s * a - dr.lim_aref; lr.lim_jv = dr.lim_s * s;
                 const T g1 = warp_sum(lane < NDOF ? s * (Ma - qfs) : T(0));
                 const T g2 = warp_sum(lane < NDOF ? T(0.5) * s * Ms : T(0));
+#ifdef GO1_DBG_LSCAP
+                const int lsmax = GO1_DBG_LSCAP;      // timing experiment only
+#else
                 const int lsmax = m.ls_iterations;
+#endif
                 int it = 0;
 #ifdef GO1_EMU_TRACE
 #define GO1_TRACE_IT g_trace_it = it
 #else
 #define GO1_TRACE_IT
 #endif
+                if (sizeof(T) == 4) {
+                    // fp32 product path: safeguarded Newton on the (continuous, increasing) derivative d1(alpha).
+                    //  * the point alpha = 0 needs no evaluation: d1(0) = grad.s and, for the exact Hessian, d2(0) = -grad.s,
+                    //    so the first trial is the full Newton move alpha = 1;
+                    //  * MuJoCo's absolute tolerance (1e-10 |s|) is below the fp32 rounding noise of d1: stop when d1 has
+                    //    dropped by GO1_LS_REL.  The Newton exit tests are unchanged, so the optimum is the same;
+                    //  * one evaluation per refinement (Newton step inside the bracket, else secant, else bisection) instead
+                    //    of MuJoCo's three.
+                    const T d10 = warp_sum(grad * s);
+                    gtol = N::max_(gtol, T(GO1_LS_REL) * N::abs_(d10));
+                    LSPoint<T> lo, hi, p;
+                    lo.alpha = 0; lo.cost = 0; lo.d1 = d10; lo.d2 = N::max_(-d10, N::MINVAL);
+                    hi = lo;
+                    bool have_hi = false;
+                    int stall = 0;
+                    p = ls_eval(m, E, lane, T(1), g1, g2, dr, lr); it++;
+#pragma unroll 1
+                    for (;;) {
+                        if (N::abs_(p.d1) < gtol) { alpha = p.alpha; break; }
+                        if (it >= (lsmax < GO1_LS_FAST_MAX ? lsmax : GO1_LS_FAST_MAX)) {
+                            // out of budget (d1 at its rounding-noise floor): the evaluated point of lowest cost; costs are
+                            // differences to alpha = 0, so a negative cost is a guaranteed decrease
+                            T best = 0;
+                            if (p.cost < best) { best = p.cost; alpha = p.alpha; }
+                            if (lo.cost < best) { best = lo.cost; alpha = lo.alpha; }
+                            if (have_hi && hi.cost < best) { best = hi.cost; alpha = hi.alpha; }
+                            break;
+                        }
+                        if (p.d1 < 0) { stall = (have_hi && N::abs_(p.d1) > T(0.5) * N::abs_(lo.d1)) ? stall + 1 : 0; lo = p; }
+                        else { stall = (have_hi && N::abs_(p.d1) > T(0.5) * N::abs_(hi.d1)) ? stall + 1 : 0; hi = p; have_hi = true; }
+                        T cand = p.alpha - p.d1 / p.d2;
+                        if (have_hi) {
+                            const T w = hi.alpha - lo.alpha;
+                            if (!(cand > lo.alpha && cand < hi.alpha)) cand = lo.alpha - lo.d1 * w / (hi.d1 - lo.d1);
+                            if (stall >= 2 || !(cand > lo.alpha && cand < hi.alpha)) { cand = lo.alpha + T(0.5) * w; stall = 0; }
+                            if (!(w > T(1e-3) * hi.alpha)) { alpha = lo.cost <= hi.cost ? lo.alpha : hi.alpha; break; }   // bracket collapsed
+                        } else if (!(cand > p.alpha)) cand = T(2) * p.alpha;
+                        p = ls_eval(m, E, lane, cand, g1, g2, dr, lr); it++;
+#ifdef GO1_EMU_TRACE
+                        if (lane == 0 && it > 10 && it < 24) std::printf("LSDBG it %d lo %.6g (%.3g) hi %.6g (%.3g) have %d cand %.8g -> d1 %.4g d2 %.4g cost %.4g gtol %.3g d10 %.3g\n", it, (double)lo.alpha, (double)lo.d1, (double)hi.alpha, (double)hi.d1, (int)have_hi, (double)cand, (double)p.d1, (double)p.d2, (double)p.cost, (double)gtol, (double)d10);
+#endif
+                    }
+                } else {
                 LSPoint<T> p0, p1, p2, pmid, p1n, p2n;
                 p0 = ls_eval(m, E, lane, T(0), g1, g2, dr, lr); it++;
                 // fp32: MuJoCo's absolute tolerance (1e-10 * |search|) is below the rounding noise of d1, the search would
@@ -1319,13 +1375,16 @@ GO1_NOINL void substep_w(const DevModel<T>& m, const EnvCfg<T>& cfg, WEnv<T>& E,
                         }
                     }
                 }
+                }
                 GO1_TRACE_IT;
             }
         }
 #ifdef GO1_EMU_TRACE
         if (lane == 0) std::printf("TRACE iter %d ncon %d lsevals %d alpha %.6g cost %.9g impr %.3g grad %.3g\n", iter, ncon, g_trace_it, (double)alpha, (double)cost, (double)improvement, (double)gradient);
 #endif
+#ifndef GO1_DBG_FIXED_ITERS
         if (alpha == 0) { conv = true; break; }
+#endif
         a += alpha * s; Ma += alpha * Ms;
         oldcost = cost;
         } while (0);

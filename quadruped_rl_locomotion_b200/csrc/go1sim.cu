@@ -64,6 +64,8 @@ struct KParams {
     T* diag; int* diag_i; T* diag_con;   // nullable
     double* stats;                 // nullable: 8 doubles
     int* queue;                    // environment queue head (zeroed before every launch)
+    const int* order;              // queue position -> environment (sorted by last step's solver work)
+    int* work;                     // per environment: Newton iterations of this control step
     unsigned long long seed, env_offset, launch_counter;
 };
 
@@ -207,8 +209,8 @@ __global__ void __launch_bounds__(GO1_WARPS * 32, GO1_MINBLOCKS) k_step(const KP
         __syncthreads();
         if (threadIdx.x == 0) s_base = atomicAdd(P.queue, GO1_WARPS);
         __syncthreads();
-        const int env = s_base + warp;
         if (s_base >= N) break;
+        const int env = s_base + warp < N ? (P.reset_only ? s_base + warp : P.order[s_base + warp]) : N;
         const bool active = env < N && !(P.reset_only && P.reset_mask && !P.reset_mask[env]);
         if (P.reset_only && !active) continue;
         if (!active) {      // keeps the block's barriers balanced
@@ -410,6 +412,7 @@ __global__ void __launch_bounds__(GO1_WARPS * 32, GO1_MINBLOCKS) k_step(const KP
             if (lane < 12) E.last_act[lane] = act;    // :529
             if (lane == 0) {
                 P.rew[env] = (float)reward;
+                P.work[env] = out.iters_total + 2 * out.ncon;
                 P.done[env] = done ? 1 : 0;
                 P.trunc[env] = (truncated && !terminated && !nonfinite) ? 1 : 0;
                 if (P.info) {
@@ -441,6 +444,20 @@ __global__ void __launch_bounds__(GO1_WARPS * 32, GO1_MINBLOCKS) k_step(const KP
         }
     }
     if (P.stats && lane < 8 && st_acc != 0.0) atomicAdd(P.stats + lane, st_acc);
+}
+
+// Queue order for the next control step: environments sorted by the solver work of the last one (counting sort,
+// heaviest first).  The warps of a block advance in lockstep, so a block is as slow as its slowest environment:
+// neighbours in the queue should need about the same number of Newton iterations.  Results do not depend on the order.
+__global__ void k_order(const int* __restrict__ work, int* __restrict__ order, int n) {
+    __shared__ int hist[256];
+    for (int i = threadIdx.x; i < 256; i += blockDim.x) hist[i] = 0;
+    __syncthreads();
+    for (int i = threadIdx.x; i < n; i += blockDim.x) { int k = work[i]; k = k < 0 ? 0 : (k > 255 ? 255 : k); atomicAdd(&hist[255 - k], 1); }
+    __syncthreads();
+    if (threadIdx.x == 0) { int acc = 0; for (int b = 0; b < 256; b++) { const int c = hist[b]; hist[b] = acc; acc += c; } }
+    __syncthreads();
+    for (int i = threadIdx.x; i < n; i += blockDim.x) { int k = work[i]; k = k < 0 ? 0 : (k > 255 ? 255 : k); order[atomicAdd(&hist[255 - k], 1)] = i; }
 }
 
 // 48-64-64-12 tanh MLP + Gaussian sampling + clip: one thread per env (weights in shared memory).
@@ -496,6 +513,7 @@ struct Go1Sim {
     bool diag_enabled = false;
     double* stats = nullptr;
     int* queue = nullptr;
+    int *order = nullptr, *work = nullptr;
     int grid_blocks = 0;
     float *d_act = nullptr, *d_obs = nullptr, *d_rew = nullptr, *d_tobs = nullptr, *d_info = nullptr;
     uint8_t *d_done = nullptr, *d_trunc = nullptr, *d_mask = nullptr;
@@ -585,7 +603,7 @@ int go1_create(const void* model_blob, size_t nbytes, const Go1EnvConfig* cfg_in
     const size_t N = (size_t)n_envs;
 #define ALLOC(p, bytes) if ((e = cudaMalloc((void**)&(p), (bytes))) != cudaSuccess) return fail("cudaMalloc " #p, e); cudaMemset((p), 0, (bytes))
     ALLOC(h->sreal, sizeof(real) * S_STRIDE * N); ALLOC(h->sint, sizeof(int) * I_STRIDE * N);
-    ALLOC(h->stats, sizeof(double) * 8); ALLOC(h->queue, sizeof(int) * 4);
+    ALLOC(h->stats, sizeof(double) * 8); ALLOC(h->queue, sizeof(int) * 4); ALLOC(h->order, sizeof(int) * N); ALLOC(h->work, sizeof(int) * N);
     ALLOC(h->d_act, sizeof(float) * 12 * N); ALLOC(h->d_obs, sizeof(float) * 48 * N); ALLOC(h->d_rew, sizeof(float) * N);
     ALLOC(h->d_tobs, sizeof(float) * 48 * N); ALLOC(h->d_info, sizeof(float) * GO1_INFO_DIM * N);
     ALLOC(h->d_done, N); ALLOC(h->d_trunc, N); ALLOC(h->d_mask, N);
@@ -623,7 +641,7 @@ int go1_destroy(go1_handle h) {
     if (!h) return GO1_EINVAL;
     cudaSetDevice(h->device);
     if (h->stream) cudaStreamSynchronize(h->stream);
-    void* dev[] = {h->queue, h->dmodel, h->sreal, h->sint, h->diag, h->diag_i, h->diag_con, h->stats, h->d_act, h->d_obs, h->d_rew, h->d_tobs,
+    void* dev[] = {h->order, h->work, h->queue, h->dmodel, h->sreal, h->sint, h->diag, h->diag_i, h->diag_con, h->stats, h->d_act, h->d_obs, h->d_rew, h->d_tobs,
                    h->d_info, h->d_done, h->d_trunc, h->d_mask, h->d_lo, h->d_hi};
     for (void* p : dev) if (p) cudaFree(p);
     void* host[] = {h->h_act, h->h_obs, h->h_rew, h->h_tobs, h->h_info, h->h_done, h->h_trunc, h->h_mask};
@@ -647,7 +665,7 @@ static KParams<real> base_params(go1_handle h) {
     KParams<real> P;
     std::memset(&P, 0, sizeof(P));
     P.model = h->dmodel; P.cfg = h->cfg; P.n_envs = h->n_envs; P.sreal = h->sreal; P.sint = h->sint;
-    P.seed = h->seed; P.env_offset = h->env_offset; P.launch_counter = h->launch_counter; P.queue = h->queue;
+    P.seed = h->seed; P.env_offset = h->env_offset; P.launch_counter = h->launch_counter; P.queue = h->queue; P.order = h->order; P.work = h->work;
     if (h->diag_enabled) { P.diag = h->diag; P.diag_i = h->diag_i; P.diag_con = h->diag_con; }
     return P;
 }
@@ -655,6 +673,13 @@ static int launch(go1_handle h, const KParams<real>& P, cudaStream_t s) {
     int grid = (h->n_envs + GO1_WARPS - 1) / GO1_WARPS;
     if (grid > h->grid_blocks) grid = h->grid_blocks;
     CK(cudaMemsetAsync(h->queue, 0, sizeof(int), s));
+    if (!P.reset_only) {
+#ifdef GO1_EMU
+        GO1_LAUNCH(k_order, 1, 32, 0, s, h->work, h->order, h->n_envs);
+#else
+        GO1_LAUNCH(k_order, 1, 1024, 0, s, h->work, h->order, h->n_envs);
+#endif
+    }
     GO1_LAUNCH(k_step<real>, grid, GO1_WARPS * 32, step_smem_bytes(), s, P);
     CK(cudaGetLastError());
     return GO1_OK;

@@ -1169,7 +1169,7 @@ GO1_NOINL void substep_w(const DevModel<T>& m, const EnvCfg<T>& cfg, WEnv<T>& E,
     const T scale = T(1) / (m.meaninertia * T(18));
     const T tol = cfg.tolerance;
     const int maxiter = cfg.solver_iterations;
-    int iter = 0, phase = 0;
+    int iter = 0, phase = 0, nstall = 0;
     T cost_s = 0, improvement = 0, gradient = 0;
     bool first = true;
     T* frc_out = capture ? con_out : (T*)nullptr;
@@ -1212,6 +1212,9 @@ GO1_NOINL void substep_w(const DevModel<T>& m, const EnvCfg<T>& cfg, WEnv<T>& E,
         grad = lane < NDOF ? Ma - qfs - qfc : T(0);
         if (!first) {
             improvement = scale * (oldcost - cnew);
+            // fp32 noise floor: a cost of magnitude c cannot resolve improvements below ~eps*c.  Heavily loaded states
+            // (tens of deep contacts, cost ~1e6) otherwise never meet the absolute tolerance and run to the iteration cap.
+            if (sizeof(T) == 4) nstall = improvement < N::max_(tol, T(2.4e-7) * scale * N::abs_(cnew)) ? nstall + 1 : 0;
             gradient = scale * N::sqrt_(warp_sum(grad * grad));
             iter++;
         }
@@ -1226,6 +1229,7 @@ GO1_NOINL void substep_w(const DevModel<T>& m, const EnvCfg<T>& cfg, WEnv<T>& E,
         // "improvement small" is only trusted when the Newton decrement -g.s/2 (the predicted improvement of the
         // next move, free of cancellation) is small too; see DESIGN.md.
         if (iter > 0 && gradient < tol) { conv = true; break; }
+        if (nstall >= 3) { conv = true; break; }
 #endif
         // ---- Hessian H = M + J'DJ (+ cone blocks), block-arrow; search = -H^-1 grad
         if (contact_stiffness(m, E, lane)) {

@@ -176,6 +176,12 @@ int go1_rollout(go1_handle h, int n_steps, int action_mode, const Go1Policy* pol
 /* elapsed device time (ms, CUDA events on the launch stream) and kernel launches of the last go1_rollout */
 int go1_last_rollout_timing(go1_handle h, float* ms, int* launches);
 
+/* Actor forward + action sampling for n rows of observations (device pointers): replaces the SB3
+ * ActorCriticPolicy forward / predict the PPO loop runs between env steps (train.py:122-128,
+ * OnPolicyAlgorithm.collect_rollouts).  log_std == NULL -> deterministic (predict(deterministic=True)).
+ * The Philox stream is (seed, env_id_offset + row, launch counter); every call advances the counter. */
+int go1_policy_act(go1_handle h, const Go1Policy* policy, const float* obs_dev, float* act_dev, int n, void* stream);
+
 int go1_set_state(go1_handle h, int env, const Go1State* s);
 int go1_get_state(go1_handle h, int env, Go1State* s);
 int go1_enable_diag(go1_handle h, int enable);       /* diag/contact capture costs HBM traffic: off by default */

@@ -215,7 +215,7 @@ __global__ void __launch_bounds__(GO1_WARPS * 32, GO1_MINBLOCKS) k_step(const KP
         if (P.reset_only && !active) continue;
         if (!active) {      // keeps the block's barriers balanced
             SubOut<T> dummy;
-            dummy.iters_total = 0; dummy.overflow = 0; dummy.bad = 0;
+            dummy.iters_total = 0; dummy.overflow = 0; dummy.bad = 0; dummy.nsub = 0; dummy.qacc = 0; dummy.qacc_prev = 0; dummy.qacc_prev2 = 0;
             for (int s = 0; s < cfg.frame_skip; s++) substep_w(m, cfg, E, lane, dummy, false, (T*)nullptr, false);
             continue;
         }
@@ -255,7 +255,7 @@ __global__ void __launch_bounds__(GO1_WARPS * 32, GO1_MINBLOCKS) k_step(const KP
             // ---- do_simulation: frame_skip x mj_step, then mj_rnePostConstraint (:481)
             SubOut<T> out;
             out.iters_total = 0; out.overflow = 0; out.bad = 0; out.ncon = 0; out.iters = 0;
-            out.qacc = 0; out.qfa = 0; out.qfc = 0; out.trunk_z = 0;
+            out.qacc = 0; out.qfa = 0; out.qfc = 0; out.trunk_z = 0; out.qacc_prev = 0; out.qacc_prev2 = 0; out.nsub = 0;
             const bool capture = P.diag_con != nullptr;
             T* con_out = capture ? P.diag_con + (size_t)env * DC_ENV : (T*)nullptr;
             {
@@ -787,6 +787,21 @@ int go1_rollout(go1_handle h, int n_steps, int action_mode, const Go1Policy* pol
         out->sum_reward = st[0]; out->n_episodes = st[1]; out->sum_episode_length = st[2]; out->sum_episode_return = st[3];
         out->n_terminated = st[4]; out->n_truncated = st[5]; out->n_bad_state = st[6]; out->env_steps = st[7];
     }
+    return GO1_OK;
+}
+
+int go1_policy_act(go1_handle h, const Go1Policy* policy, const float* obs_dev, float* act_dev, int n, void* stream) {
+    if (!h || !policy || !obs_dev || !act_dev || n < 0) return GO1_EINVAL;
+    CK(cudaSetDevice(h->device));
+    cudaStream_t s = stream ? (cudaStream_t)stream : h->stream;
+    if (n == 0) return GO1_OK;
+#ifdef GO1_EMU
+    const int tb = 1;
+#else
+    const int tb = 128;
+#endif
+    GO1_LAUNCH(k_policy, (n + tb - 1) / tb, tb, 0, s, obs_dev, act_dev, n, *policy, h->d_lo, h->d_hi, h->seed, h->launch_counter, h->env_offset);
+    h->launch_counter++;
     return GO1_OK;
 }
 

@@ -69,7 +69,7 @@ class Policy(C.Structure):
 
 EXPORTS = (
     "go1_default_config", "go1_precision_bits", "go1_version", "go1_create", "go1_destroy", "go1_last_error",
-    "go1_num_envs", "go1_action_bounds", "go1_reset", "go1_step", "go1_step_host", "go1_reset_host", "go1_rollout",
+    "go1_num_envs", "go1_action_bounds", "go1_reset", "go1_step", "go1_step_host", "go1_reset_host", "go1_rollout", "go1_policy_act",
     "go1_last_rollout_timing", "go1_set_state", "go1_get_state", "go1_enable_diag", "go1_get_diag",
     "go1_get_contacts", "go1_set_attr_f32", "go1_get_attr_f32",
 )
@@ -107,6 +107,7 @@ class Go1Lib:
         L.go1_step_host.argtypes = [vp, f32p, f32p, f32p, u8p, u8p, f32p, f32p]
         L.go1_reset_host.argtypes = [vp, u8p, f32p]
         L.go1_rollout.argtypes = [vp, i32, i32, C.POINTER(Policy), C.POINTER(Stats), vp]
+        L.go1_policy_act.argtypes = [vp, C.POINTER(Policy), f32p, f32p, i32, vp]
         L.go1_last_rollout_timing.argtypes = [vp, C.POINTER(C.c_float), C.POINTER(C.c_int)]
         L.go1_set_state.argtypes = [vp, i32, C.POINTER(State)]
         L.go1_get_state.argtypes = [vp, i32, C.POINTER(State)]
@@ -205,6 +206,11 @@ class Sim:
         out = {k: getattr(st, k) for k, _ in Stats._fields_}
         out["device_ms"] = float(ms.value); out["launches"] = int(launches.value)
         return out
+
+    def policy_act(self, policy: Policy, obs, act, n: int | None = None, stream=None):
+        """Actor forward + sampling on device buffers (``go1_policy_act``)."""
+        self._check(self.lib.L.go1_policy_act(self._h, C.byref(policy), _ptr(obs), _ptr(act),
+                                              int(self.n_envs if n is None else n), stream), "go1_policy_act")
 
     # -- state / diagnostics
     def set_state(self, env: int, **kw):

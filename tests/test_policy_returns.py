@@ -1,0 +1,85 @@
+"""north_star correctness part 3: the reference's SHIPPED policies reach the same mean episode return in the CUDA
+simulator as in the reference environment (trajectories are chaotic, so only statistics are comparable).
+
+Reference arm = ``tests/golden/returns_<tag>.npz``: 1000 seeded episodes of the unmodified ``go1_mujoco_env.py``
+on the fp64 oracle physics (``tests/golden/make_returns.py``; episodes capped at ``max_steps`` control steps,
+deterministic actions, desired velocity (0.5, 0, 0), 20 % fallen starts left on, reset joint noise rand_power = 1
+so that the upright starts form an ensemble instead of one deterministic trajectory).  Our arm = the same protocol
+through ``Go1CudaVecEnv.step`` (host policy, host buffers) with many more episodes so that its own sampling
+error is negligible.  The bar is |mean_ours - mean_ref| <= max(2 % of mean_ref, 3 standard errors of the
+1000-episode reference mean): with 1000 episodes the reference mean itself is only known to ~1-1.5 %
+(bimodal returns: fallen vs upright starts), so a pure 2 % test would fail by chance; the two start strata are
+also compared separately."""
+import os
+
+import numpy as np
+import pytest
+
+import parity_common as pc
+from quadruped_rl_locomotion_b200.vec_env import Go1CudaVecEnv
+
+TAGS = ("pos_0428", "pos_0421")
+
+
+def _policy(tag):
+    w = dict(np.load(os.path.join(pc.GOLDEN, f"policy_{tag}.npz")))
+
+    def act(obs, lo, hi):
+        x = obs.astype(np.float32)
+        h = np.tanh(x @ w["w0"].T + w["b0"]); h = np.tanh(h @ w["w1"].T + w["b1"])
+        return np.clip(h @ w["w2"].T + w["b2"], lo, hi).astype(np.float32)
+    return act
+
+
+def run_episodes(lib, tag, n_envs, max_steps, seed=0, rand_power=1.0):
+    """First episode of every env, capped at max_steps: returns (ret, length, fallen_start)."""
+    env = Go1CudaVecEnv(n_envs, ctrl_type="position", rand_power=rand_power, library=lib, seed=seed, desired_velocity_min=(0.5, 0, 0),
+                        desired_velocity_max=(0.5, 0, 0))
+    act = _policy(tag)
+    lo, hi = env.action_space.low, env.action_space.high
+    obs = env.reset()
+    assert np.allclose(obs[:, 9:12], [1.0, 0, 0])                     # the "x=1" target in the scaled observation
+    fallen = np.array([abs(env.sim.get_state(e)["qpos"][2] - 0.1) < 1e-6 for e in range(n_envs)])
+    ret = np.zeros(n_envs); length = np.zeros(n_envs, int); alive = np.ones(n_envs, bool)
+    for _ in range(max_steps):
+        obs, rew, dones, _ = env.step(act(obs, lo, hi))
+        ret += np.where(alive, rew, 0.0); length += alive
+        alive &= ~dones
+        if not alive.any():
+            break
+    env.close()
+    return ret, length, fallen
+
+
+def test_protocol_smoke_emu(emu_lib_f32):
+    """CPU: the evaluation harness itself (few envs, few steps) on the emulation build."""
+    ret, length, fallen = run_episodes(emu_lib_f32, "pos_0428", 6, 12)
+    assert np.all(length == 12) and np.all(ret >= 0) and np.isfinite(ret).all()
+    ref = np.load(os.path.join(pc.GOLDEN, "returns_pos_0428.npz"))
+    assert len(ref["ret"]) >= 1000 and abs(ref["fallen"].mean() - 0.2) < 0.04
+    assert np.allclose(ref["v_des"], [0.5, 0, 0])
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("tag", TAGS)
+def test_shipped_policy_mean_return(cuda_lib_f32, tag):
+    ref = np.load(os.path.join(pc.GOLDEN, f"returns_{tag}.npz"))
+    max_steps = int(ref["max_steps"])
+    ret, length, fallen = run_episodes(cuda_lib_f32, tag, 8192, max_steps, seed=2024, rand_power=float(ref["rand_power"]))
+    r_ref, f_ref = ref["ret"], ref["fallen"] > 0.5
+    se = r_ref.std() / np.sqrt(len(r_ref))
+    tol = max(0.02 * r_ref.mean(), 3 * se)
+    print(f"{tag}: ours {ret.mean():.2f} (n={len(ret)}, fallen {fallen.mean():.3f}, len {length.mean():.0f}) | reference "
+          f"{r_ref.mean():.2f} +- {se:.2f} (n={len(r_ref)}, fallen {f_ref.mean():.3f}, len {ref['length'].mean():.0f}) | "
+          f"rel diff {(ret.mean() - r_ref.mean()) / r_ref.mean():+.4f}, tol {tol / r_ref.mean():.4f}")
+    for name, mo, mr in (("upright", ~fallen, ~f_ref), ("fallen", fallen, f_ref)):
+        se_s = r_ref[mr].std() / np.sqrt(mr.sum())
+        d = ret[mo].mean() - r_ref[mr].mean()
+        print(f"   {name:8s} ours {ret[mo].mean():.2f} | reference {r_ref[mr].mean():.2f} +- {se_s:.2f} | rel diff {d / r_ref[mr].mean():+.4f}")
+        assert abs(d) <= max(0.02 * abs(r_ref[mr].mean()), 3.5 * se_s), name
+    assert abs(fallen.mean() - 0.2) < 0.02
+    # stratified mean with the nominal 20/80 start mix removes the binomial noise of the fallen fraction
+    strat_o = 0.2 * ret[fallen].mean() + 0.8 * ret[~fallen].mean()
+    strat_r = 0.2 * r_ref[f_ref].mean() + 0.8 * r_ref[~f_ref].mean()
+    assert abs(strat_o - strat_r) <= tol
+    assert abs(ret.mean() - r_ref.mean()) <= tol

@@ -28,11 +28,15 @@ def main():
     obs = np.zeros((n, 48), np.float32); rew = np.zeros(n, np.float32)
     done = np.zeros(n, np.uint8); trunc = np.zeros(n, np.uint8)
     tobs = np.zeros((n, 48), np.float32); info = np.zeros((n, 16), np.float32)
+    dump = os.environ.get("GO1_ITER_DUMP")
+    hist_it, hist_nc = [], []
     for t in range(steps):
         a = rng.uniform(lo, hi, size=(n, 12)).astype(np.float32)
         t0 = time.perf_counter()
         sim.step_host(a, obs, rew, done, trunc, tobs, info)
         dt = time.perf_counter() - t0
+        if dump:
+            hist_it.append(info[:, 14].copy()); hist_nc.append(info[:, 15].copy())
         if t % 10 == 0 or t == steps - 1:
             it = info[:, 14]; nc = info[:, 15]
             q = np.percentile(it, [0, 50, 90, 99, 100])
@@ -40,6 +44,8 @@ def main():
             wmax = it.reshape(-1, 8).max(axis=1)
             print(f"step {t:4d} {dt*1e3:7.2f} ms | iters/ctrl-step min/med/p90/p99/max {q} mean {it.mean():.1f} warp-max mean {wmax.mean():.1f}"
                   f" | ncon med {np.median(nc):.0f} max {nc.max():.0f} mean {nc.mean():.2f} | healthy {info[:,13].mean():.3f} done {done.sum()}")
+    if dump:
+        np.savez_compressed(dump, iters=np.array(hist_it, np.int16), ncon=np.array(hist_nc, np.int16))
     sim.close()
 
 

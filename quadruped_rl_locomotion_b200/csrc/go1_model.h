@@ -5,6 +5,7 @@
 // trunk + NLEG identical 3-hinge chains.  build_dev_model() validates exactly that and refuses
 // anything else loudly (GO1_EMODEL) instead of guessing.
 #pragma once
+#include <algorithm>
 #include <cmath>
 #include <cstdint>
 #include <cstring>
@@ -45,6 +46,7 @@ struct DevClass {
 template <typename T>
 struct DevModel {
     T timestep, gravity[3], impratio, tolerance, ls_tolerance, meaninertia, total_mass;
+    T lambda_lb;     // rigorous lower bound of the eigenvalues of M (any pose): min(leg armature, trunk mass, trunk principal inertias)
     int iterations, ls_iterations, nclass, pad0;
     T plane_pos[3], plane_frame[9];
     // trunk
@@ -196,6 +198,10 @@ inline bool build_dev_model(const void* data, size_t nbytes, DevModel<double>& M
     M.t_mass = body_mass[1];
     for (int c = 0; c < 3; c++) M.t_ipos[c] = body_ipos[3 + c];
     body_inertia(body_iquat + 4, body_inertia_ + 3, M.t_Ib);
+    // M = sum_b J_b' I_b J_b + diag(armature) >= J_trunk' I_trunk J_trunk + diag(armature): block diagonal (trunk spatial inertia,
+    // armature on the 12 hinges), so lambda_min(M) >= min(trunk mass, smallest trunk principal inertia, smallest armature)
+    M.lambda_lb = std::min(body_mass[1], std::min(body_inertia_[3], std::min(body_inertia_[4], body_inertia_[5])));
+    for (int d = 6; d < 18; d++) M.lambda_lb = std::min(M.lambda_lb, dof_armature[d]);
     M.t_invw[0] = body_invw[2]; M.t_invw[1] = body_invw[3];
     for (int k = 0; k < NLEG; k++)
         for (int i = 0; i < 3; i++) {
@@ -399,7 +405,7 @@ inline void cast_dev_model(const DevModel<double>& S, DevModel<T>& D) {
 #define CP(f) D.f = (T)S.f
 #define CPA(f) do { const double* s_ = (const double*)&S.f; T* d_ = (T*)&D.f; for (size_t i_ = 0; i_ < sizeof(S.f) / sizeof(double); i_++) d_[i_] = (T)s_[i_]; } while (0)
 #define CPI(f) std::memcpy(&D.f, &S.f, sizeof(S.f))
-    CP(timestep); CPA(gravity); CP(impratio); CP(tolerance); CP(ls_tolerance); CP(meaninertia); CP(total_mass);
+    CP(timestep); CPA(gravity); CP(impratio); CP(tolerance); CP(ls_tolerance); CP(meaninertia); CP(total_mass); CP(lambda_lb);
     CP(iterations); CP(ls_iterations); CP(nclass);
     CPA(plane_pos); CPA(plane_frame); CP(t_mass); CPA(t_ipos); CPA(t_Ib); CPA(t_invw);
     CPA(body_pos); CPA(jnt_axis); CPA(ipos); CPA(mass); CPA(Ib); CPA(invw); CPA(qpos0); CPA(damping); CPA(armature);

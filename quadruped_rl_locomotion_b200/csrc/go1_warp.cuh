@@ -38,6 +38,9 @@ constexpr int NDOF = 18;    // 0..5 trunk (3 lin world, 3 rot body frame), 6 + 3
 #ifndef GO1_WARM_EXTRAP
 #define GO1_WARM_EXTRAP 1     // fp32 build: warm start = 2 a(t-1) - a(t-2) inside a control step (see substep_w)
 #endif
+#ifndef GO1_GRAD_BOUND_EXIT
+#define GO1_GRAD_BOUND_EXIT 1
+#endif
 #ifndef GO1_SKIP_SMOOTH_CHECK
 #define GO1_SKIP_SMOOTH_CHECK 1
 #endif
@@ -1260,6 +1263,11 @@ GO1_NOINL void substep_w(const DevModel<T>& m, const EnvCfg<T>& cfg, WEnv<T>& E,
         // "improvement small" is only trusted when the Newton decrement -g.s/2 (the predicted improvement of the
         // next move, free of cancellation) is small too; see DESIGN.md.
         if (iter > 0 && gradient < tol) { conv = true; break; }
+        // fp32: |grad| never reaches MuJoCo's 1e-8 (rounding floor of M a - qfrc), but H >= M >= lambda_lb*I bounds the Newton
+        // decrement from the gradient alone: g'H^-1 g / 2 <= |g|^2 / (2 lambda_lb).  If even that bound is below the
+        // tolerance the point is converged and the Hessian assembly / factorisation / solve of this round are skipped.
+        if (GO1_GRAD_BOUND_EXIT && sizeof(T) == 4 && iter > 0 && m.lambda_lb > 0 &&
+            T(0.5) * gradient * gradient < tol * scale * m.lambda_lb) { conv = true; break; }
         if (nstall >= 3) { conv = true; break; }
 #endif
         // ---- Hessian H = M + J'DJ (+ cone blocks), block-arrow; search = -H^-1 grad

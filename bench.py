@@ -29,6 +29,9 @@ UNIT = "env-steps/s"
 ENVS_PER_GPU = 16384
 ALG_BYTES_PER_ENV_STEP = 904.0     # 82 state words r+w, 12 action floats in, obs/reward/flags out
 ALG_FLOP_PER_ENV_STEP = 0.67e6     # SURVEY 8(d) nominal (10 substeps x (25k + 3 Newton iterations x 14k))
+# dram__bytes_read.sum + dram__bytes_write.sum of ONE k_step launch at 16384 envs, from the committed ncu --set full capture
+# (profiles/r1_ncu_k_step_warp2_raw_selected.txt): 9.05 MB + 12.08 MB
+NCU_DRAM_BYTES_PER_LAUNCH_16K = 21.13e6
 
 
 def _peaks():
@@ -244,8 +247,10 @@ def run_ours(args, rank, world, local):
                        "envs_per_gpu": n, "parallelism": f"env-slab x{world} (no data-path collective)",
                        "l2": "flushed between timed steps (256 MiB write, untimed)", "timing": "CUDA events on the launch stream, max over ranks"},
             "roofline": {"bound": "hbm", "achieved": ach_gbs, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": ach_gbs / peaks["hbm_gbs"],
-                         "traffic": None, "peak_source": pk,
-                         "note": "HBM is not the binding roof (904 B/env-step); see fp32 block",
+                         "traffic": NCU_DRAM_BYTES_PER_LAUNCH_16K if (n == ENVS_PER_GPU and args.ctrl == "torque") else None,
+                         "algorithmic_bytes_per_launch": ALG_BYTES_PER_ENV_STEP * n, "peak_source": pk,
+                         "note": "neither HBM nor FP32 binds: the GPC instruction cache does (gcc instruction requests at 80 % of "
+                                 "peak, DESIGN.md section 3); see fp32 block",
                          "fp32": {"achieved_tflops": ach_tf, "peak_tflops": fp32_peak, "frac": ach_tf / fp32_peak,
                                   "flop_per_env_step": ALG_FLOP_PER_ENV_STEP, "peak": "n_SM*128*2*f_max (nominal)", "sm_mhz_under_load": sm_mhz}},
             "cpu_baseline": {"value": cpu_v, "unit": UNIT, "cores": cores, "kind": "port",

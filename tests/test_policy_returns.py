@@ -1,13 +1,13 @@
 """north_star correctness part 3: the reference's SHIPPED policies reach the same mean episode return in the CUDA
 simulator as in the reference environment (trajectories are chaotic, so only statistics are comparable).
 
-Reference arm = ``tests/golden/returns_<tag>.npz``: 1000 seeded episodes of the unmodified ``go1_mujoco_env.py``
+Reference arm = ``tests/golden/returns_<tag>.npz``: 4000 seeded episodes of the unmodified ``go1_mujoco_env.py``
 on the fp64 oracle physics (``tests/golden/make_returns.py``; episodes capped at ``max_steps`` control steps,
 deterministic actions, desired velocity (0.5, 0, 0), 20 % fallen starts left on, reset joint noise rand_power = 1
 so that the upright starts form an ensemble instead of one deterministic trajectory).  Our arm = the same protocol
 through ``Go1CudaVecEnv.step`` (host policy, host buffers) with many more episodes so that its own sampling
 error is negligible.  The bar is |mean_ours - mean_ref| <= max(2 % of mean_ref, 3 standard errors of the
-1000-episode reference mean): with 1000 episodes the reference mean itself is only known to ~1-1.5 %
+reference mean): with 4000 episodes the reference mean itself is only known to ~1.6 %
 (bimodal returns: fallen vs upright starts), so a pure 2 % test would fail by chance; the two start strata are
 also compared separately."""
 import os

@@ -145,3 +145,25 @@ def test_vec_env_gpu(cuda_lib_f32):
     env = Go1CudaVecEnv(8, library=cuda_lib_f32, seed=3)
     _auto_reset(env, 8)
     env.close()
+
+
+def test_reset_joint_noise_emu(emu_lib_f32):
+    """rand_power > 0 (go1_mujoco_env.py:974-982): joint noise N(0, 0.1 * rand_power) on the keyframe joints, clipped
+    to jnt_range; the curriculum callback changes it through set_attr (training_callback.py:64)."""
+    n = 3000
+    cfg = emu_lib_f32.default_config(); cfg.rand_power = 1.0; cfg.fallen_start_prob = 0.0
+    sim = L.Sim(pc.model_blob("position"), n, lib=emu_lib_f32, cfg=cfg, seed=21)
+    sim.reset_host()
+    q = np.array([sim.get_state(e)["qpos"][7:] for e in range(n)])
+    home = np.tile([0, 0.9, -1.8], 4)
+    lo, hi = sim.action_bounds()                      # position model: ctrlrange == jnt_range
+    d = q - home
+    assert np.all(q >= lo - 1e-6) and np.all(q <= hi + 1e-6)
+    free = [0, 3, 6, 9, 1, 4, 7, 10]                  # abduction / hip joints: the range is far from the keyframe value
+    assert abs(d[:, free].mean()) < 0.01 and abs(d[:, free].std() - 0.1) < 0.01
+    assert abs(np.corrcoef(d[:, 0], d[:, 1])[0, 1]) < 0.08
+    sim.set_attr("rand_power", 0.5)
+    sim.reset_host()
+    q2 = np.array([sim.get_state(e)["qpos"][7:] for e in range(n)])
+    assert abs((q2 - home)[:, free].std() - 0.05) < 0.006
+    sim.close()

@@ -43,6 +43,7 @@ extern "C" {
 #define GO1_NV 18
 #define GO1_NBODY 14
 #define GO1_INFO_DIM 16
+#define GO1_BIPED_INFO_DIM 12
 #define GO1_MAX_CONTACTS 64
 
 enum {
@@ -51,13 +52,13 @@ enum {
     GO1_EMODEL = -2,      /* model blob rejected (format / unsupported topology or feature) */
     GO1_ECUDA = -3,       /* CUDA runtime error */
     GO1_ENOMEM = -4,
-    GO1_EUNSUPPORTED = -5 /* e.g. biped=1 */
+    GO1_EUNSUPPORTED = -5 /* e.g. a model the kernel layout does not cover, biped info without biped mode */
 };
 
 /* Environment constants; zero-initialise then call go1_default_config() to obtain the
  * reference's literals (go1_mujoco_env.py:64-150). */
 typedef struct Go1EnvConfig {
-    int32_t biped;                 /* go1_mujoco_env.py:41; must be 0 (biped terms: DESIGN.md "next") */
+    int32_t biped;                 /* go1_mujoco_env.py:41,:43: 1 = bipedal mode (reset pose :967-972, terms :869-904) */
     int32_t frame_skip;            /* :49  -> 10 */
     int32_t max_episode_steps;     /* :64,:498 -> 6000 */
     int32_t max_unhealthy_steps;   /* :130,:497 -> terminate at the 751st consecutive unhealthy step: 750 */
@@ -76,7 +77,12 @@ typedef struct Go1EnvConfig {
     float obs_clip;                /* :150 */
     float solver_tolerance;        /* <0: use the model's (MJCF <option tolerance>) */
     int32_t solver_iterations;     /* <=0: use the model's */
-    int32_t reserved[8];
+    float biped_w[10];             /* :92-101 biped_upright (reward); front_contact, rear_feet_airborne, front_foot_height,
+                                             crossed_legs, low_rear_hips, front_feet_below_hips, abduction_joints,
+                                             unwanted_contact, self_collision (costs).  Read only when biped != 0. */
+    float biped_ready_joints[12];  /* :32-39 BIPEDAL_READY_JOINTS (FR, FL, RR, RL) */
+    float biped_reset_z;           /* :969 -> 0.65 */
+    float biped_reset_pitch_deg;   /* :970 -> -95 */
 } Go1EnvConfig;
 
 /* Full per-environment state for teacher-forced parity tests (doubles in both builds). */
@@ -94,6 +100,8 @@ typedef struct Go1State {
     int32_t unhealthy_steps;
     int32_t reset_count;
     int32_t bad_state;
+    int32_t front_feet_touched;    /* :66,:477-479 (biped only) */
+    int32_t pad_;
 } Go1State;
 
 /* What mjData holds after do_simulation, as the reference reads it. */
@@ -181,6 +189,15 @@ int go1_last_rollout_timing(go1_handle h, float* ms, int* launches);
  * OnPolicyAlgorithm.collect_rollouts).  log_std == NULL -> deterministic (predict(deterministic=True)).
  * The Philox stream is (seed, env_id_offset + row, launch counter); every call advances the counter. */
 int go1_policy_act(go1_handle h, const Go1Policy* policy, const float* obs_dev, float* act_dev, int n, void* stream);
+
+/* Biped mode only (cfg.biped != 0; GO1_EUNSUPPORTED otherwise): the extra reward_info entries of the LAST control
+ * step, out[N][GO1_BIPED_INFO_DIM] f32 HOST buffer (synchronous D2H): biped_upright_reward, biped_front_contact_cost,
+ * biped_rear_feet_airborne_cost, biped_front_foot_height_cost, biped_crossed_legs_cost, biped_low_rear_hips_cost,
+ * biped_front_feet_below_hips_cost, biped_abduction_joints_cost, biped_unwanted_contact_cost, self_collision_cost
+ * (go1_mujoco_env.py:893-902, costs negated as there), bipedal_success (:520-521), front_feet_touched (:477-479).
+ * go1_biped_info_dev returns the device pointer of the same rows for device-resident callers. */
+int go1_biped_info_host(go1_handle h, float* out);
+int go1_biped_info_dev(go1_handle h, const float** ptr);
 
 int go1_set_state(go1_handle h, int env, const Go1State* s);
 int go1_get_state(go1_handle h, int env, Go1State* s);

@@ -37,6 +37,17 @@ CONTACT_BODIES = [2, 3, 5, 6, 8, 9, 11, 12]            # :126
 DT = 0.02                                              # timestep 0.002 * frame_skip 10
 MAX_UNHEALTHY_TIME = 15.0                              # :130
 MAX_EPISODE_STEPS = 120.0 / DT                         # :64, :498
+BIPED_REWARD_WEIGHT = 15.0                              # :92  biped_upright
+BIPED_COST_WEIGHTS = {  # :93-101
+    "front_contact": 50.0, "rear_feet_airborne": 5.0, "front_foot_height": 8.0, "crossed_legs": 5.0, "low_rear_hips": 9.0,
+    "front_feet_below_hips": 6.0, "abduction_joints": 0.7, "unwanted_contact": 150.0, "self_collision": 25.0,
+}
+BIPEDAL_READY_JOINTS = np.array([0.0, 4.0, -2.0, 0.0, 4.0, -2.0, 0.0, 2.8, -1.2, 0.0, 2.8, -1.2])   # :32-39
+UNWANTED_CONTACT_BODIES = [1, 3, 6, 9, 12, 4, 7]       # :192-200 trunk, thighs, front calves (MuJoCo body ids)
+BIPED_INFO_KEYS = ("biped_upright_reward", "biped_front_contact_cost", "biped_rear_feet_airborne_cost",
+                   "biped_front_foot_height_cost", "biped_crossed_legs_cost", "biped_low_rear_hips_cost",
+                   "biped_front_feet_below_hips_cost", "biped_abduction_joints_cost", "biped_unwanted_contact_cost",
+                   "self_collision_cost")
 INFO_KEYS = ("linear_vel_tracking_reward", "reward_ctrl", "reward_survive", "recovery_reward", "get_up_reward",
              "unhealthy_state_cost", "orientation_cost", "default_joint_position_cost")
 
@@ -92,12 +103,14 @@ class EpisodeState:
     desired_velocity: np.ndarray = field(default_factory=lambda: np.zeros(3))
     time_unhealthy: float = 0.0
     last_dev: np.ndarray = field(default_factory=lambda: np.zeros(3))  # z, roll, pitch
+    front_feet_touched: bool = False                                   # biped only (:476-479)
 
 
 class EnvLogic:
     """Per-step env logic given the physics results of ``do_simulation``."""
 
-    def __init__(self, model):
+    def __init__(self, model, biped=False):
+        self.biped = bool(biped)
         self.key_qpos = np.array(model.key_qpos[0])
         self.default_joint_position = np.array(model.key_ctrl[0])      # :105
         self.soft_range = soft_joint_range(np.array(model.actuator_ctrlrange))
@@ -110,7 +123,8 @@ class EnvLogic:
         ])
         return np.clip(o, -100.0, 100.0)
 
-    def step(self, ep: EpisodeState, action, qpos, qvel, qacc, qfrc_actuator, cfrc_ext, trunk_z_xpos):
+    def step(self, ep: EpisodeState, action, qpos, qvel, qacc, qfrc_actuator, cfrc_ext, trunk_z_xpos, kin=None,
+             prev_front_feet_forces=None, n_self_collisions=0):
         """Everything ``Go1MujocoEnv.step`` does after ``do_simulation`` (:483-532).
 
         ``qpos/qvel`` are post-step; ``qacc/qfrc_actuator/cfrc_ext/trunk_z_xpos`` are the values MuJoCo
@@ -119,6 +133,8 @@ class EnvLogic:
         """
         action = np.asarray(action, dtype=np.float64)
         ep.step += 1                                                    # :474
+        if self.biped and prev_front_feet_forces is not None and np.any(np.asarray(prev_front_feet_forces) > 1.0):
+            ep.front_feet_touched = True                                # :477-479: cfrc_ext of the PREVIOUS step
         obs = self.obs(qpos, qvel, ep)                                  # :483 (last_action = a_{t-1})
         ok, reason = health(qpos, qvel)
         pg = projected_gravity(qpos[3:7], self.gravity)
@@ -130,13 +146,16 @@ class EnvLogic:
         # feet air time (:633-668)
         feet_f = np.linalg.norm(cfrc_ext[FEET_BODIES], axis=1)
         curr = feet_f > 1.0
-        filt = np.logical_or(curr, ep.last_contacts)
-        ep.last_contacts = curr.copy()
-        first = (ep.feet_air_time > 0.0) * filt
-        ep.feet_air_time = ep.feet_air_time + DT
-        air = np.sum(np.square((ep.feet_air_time - 0.2).clip(min=0.0)) * first)
-        air *= np.linalg.norm(v_des[:2]) > 0.1
-        ep.feet_air_time = ep.feet_air_time * ~filt
+        if self.biped:                                                  # :646-649: alternating rear feet, no bookkeeping
+            air = float(curr[2] != curr[3])
+        else:
+            filt = np.logical_or(curr, ep.last_contacts)
+            ep.last_contacts = curr.copy()
+            first = (ep.feet_air_time > 0.0) * filt
+            ep.feet_air_time = ep.feet_air_time + DT
+            air = np.sum(np.square((ep.feet_air_time - 0.2).clip(min=0.0)) * first)
+            air *= np.linalg.norm(v_des[:2]) > 0.1
+            ep.feet_air_time = ep.feet_air_time * ~filt
         air_r = air * REWARD_WEIGHTS["feet_airtime"]
         # recovery (:534-580)
         z, roll, pitch = qpos[2], qpos[4], qpos[5]
@@ -175,7 +194,26 @@ class EnvLogic:
         unh_c = (0.0 if ok else 1.0) * COST_WEIGHTS["unhealthy_state"]
         orient_c = np.sum(np.square(pg[:2])) * COST_WEIGHTS["orientation"]
         djp_c = np.sum(np.square(qpos[7:] - self.default_joint_position)) * COST_WEIGHTS["default_joint_position"]
-        costs = ctrl_c + rate_c + vert_c + xyang_c + jl_c + jv_c + acc_c + coll_c + unh_c + orient_c + djp_c
+        costs = ctrl_c + rate_c + vert_c + xyang_c + jl_c + jv_c + acc_c + coll_c + unh_c
+        binfo = {}
+        if self.biped:                                                  # :869-904
+            w = BIPED_COST_WEIGHTS
+            front_f = feet_f[:2]
+            up = max(0.0, float(kin["trunk_xaxis_z"])) * BIPED_REWARD_WEIGHT                      # :388-401
+            fc = float(np.sum(np.square(front_f))) * w["front_contact"]                              # :426-431
+            ra = w["rear_feet_airborne"] if np.all(feet_f[2:] < 1.0) else 0.0                        # :880-882
+            fh = float(np.sum((kin["front_calf_z"] - kin["front_feet_z"]).clip(min=0.0))) * w["front_foot_height"]   # :403-423
+            cl = max(0.0, float(kin["rear_hip_y"][0] - kin["rear_hip_y"][1])) * w["crossed_legs"]    # :315-331
+            lh = float(np.sum((0.2 - kin["rear_hip_z"]).clip(min=0.0))) * 10.0 * w["low_rear_hips"]  # :334-351
+            fb = float(np.sum(np.square((kin["front_hip_z"] - kin["front_feet_z"]).clip(min=0.0)))) * w["front_feet_below_hips"]  # :354-376
+            ab = float(np.sum(np.square(qpos[7:][[0, 3, 6, 9]]))) * w["abduction_joints"]            # :759-769
+            uc = float(np.sum(np.square(np.linalg.norm(cfrc_ext[UNWANTED_CONTACT_BODIES], axis=1)))) * w["unwanted_contact"]  # :772-781
+            sc = float(n_self_collisions) * w["self_collision"]                                      # :269-312
+            rewards = rewards + up
+            costs = costs + fc + ra + fh + cl + lh + fb + ab + uc + sc
+            binfo = dict(zip(BIPED_INFO_KEYS, (up, -fc, -ra, -fh, -cl, -lh, -fb, -ab, -uc, -sc)))
+        else:
+            costs = costs + orient_c + djp_c
         reward = max(0.0, rewards - costs)                              # :911
         # ---- termination (:487-498)
         if not ok:
@@ -189,7 +227,8 @@ class EnvLogic:
             "linear_vel_tracking_reward": lin, "reward_ctrl": -ctrl_c, "reward_survive": healthy_r,
             "recovery_reward": rec_r, "get_up_reward": gu_r, "unhealthy_state_cost": -unh_c,
             "orientation_cost": -orient_c, "default_joint_position_cost": -djp_c,
-            "feet_contact_forces": feet_f,
+            "feet_contact_forces": feet_f, **binfo,
+            "bipedal_success": bool(truncated and self.biped and not ep.front_feet_touched),         # :520-521
         }
         ep.last_action = action.copy()                                  # :529
         return obs, reward, terminated, truncated, info

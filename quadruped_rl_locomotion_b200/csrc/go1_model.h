@@ -398,6 +398,24 @@ inline bool build_dev_model(const void* data, size_t nbytes, DevModel<double>& M
     return true;
 }
 
+// Foot sites (the first site attached to each calf; go1.xml names them FR, FL, RR, RL): position in the calf frame.
+// Only the biped terms read them (go1_mujoco_env.py:360, :409), so they travel in EnvCfg, not in DevModel.
+inline bool read_foot_sites(const void* data, size_t nbytes, double out[NLEG][3], std::string& err) {
+    Blob blob; blob.b = (const uint8_t*)data; blob.n = nbytes;
+    int ns = 0;
+    const int* bodyid = blob.i("site_bodyid", &ns);
+    const double* pos = blob.d("site_pos");
+    if (!bodyid || !pos) { err = blob.err; return false; }
+    for (int k = 0; k < NLEG; k++) {
+        int found = -1;
+        for (int s = 0; s < ns && found < 0; s++)
+            if (bodyid[s] == 4 + 3 * k) found = s;      // MuJoCo body ids: world 0, trunk 1, leg k: hip 2+3k, thigh 3+3k, calf 4+3k
+        if (found < 0) { err = "model has no foot site on a calf body"; return false; }
+        for (int e = 0; e < 3; e++) out[k][e] = pos[3 * found + e];
+    }
+    return true;
+}
+
 template <typename T>
 inline void cast_dev_model(const DevModel<double>& S, DevModel<T>& D) {
     // field-wise cast: both structs have identical layout up to the scalar type, walk them as arrays

@@ -457,7 +457,14 @@ struct EnvCfg {
     int frame_skip, max_episode_steps, max_unhealthy_steps, solver_iterations;
     T rand_power, fallen_prob, vdes_min[3], vdes_max[3], reward_w[6], cost_w[11];
     T healthy_z[2], healthy_roll[2], healthy_pitch[2], sigma, obs_clip, tolerance;
+    // bipedal mode (go1_mujoco_env.py:43, :91-101, :967-972); read only when biped != 0
+    int biped;
+    T biped_w[10], biped_reset_z, biped_reset_qw, biped_reset_qy, foot_site[2][3];
+    const T* biped_ready;      // device array [12] (indexed by lane: kept out of the kernel parameters, which must not be indexed dynamically)
 };
+
+// kinematic quantities the biped terms read from mjData (world frame, start of the last substep), one row per env
+enum { BK_HIP_Z = 0 /* FR FL RR RL */, BK_REAR_HIP_Y = 4 /* RR RL */, BK_FRONT_CALF_Z = 6, BK_FRONT_FOOT_Z = 8, BK_TRUNK_XZ = 10, BK_N = 12 };
 
 // what mjData holds after the last substep, as the env reads it (per-lane registers + E.cfrc)
 template <typename T> struct SubOut {
@@ -909,7 +916,7 @@ GO1_NOINL LSPoint<T> ls_eval(const DevModel<T>& m, const WEnv<T>& E, int lane, T
 // one physics substep (mj_step) of the environment owned by this warp
 template <typename T>
 GO1_NOINL void substep_w(const DevModel<T>& m, const EnvCfg<T>& cfg, WEnv<T>& E, const int lane, SubOut<T>& out,
-                         const bool capture, T* con_out, const bool active) {
+                         const bool capture, T* con_out, const bool active, T* bip_out = nullptr) {
     typedef Num<T> N;
     const T h = m.timestep;
     const int jl = lane >= 6 && lane < NDOF ? lane - 6 : 0;      // leg-dof index of this lane (0..11)
@@ -987,6 +994,18 @@ GO1_NOINL void substep_w(const DevModel<T>& m, const EnvCfg<T>& cfg, WEnv<T>& E,
             for (int e = 0; e < 9; e++) E.xmat()[mybody][e] = Rb[e];
 #pragma unroll
             for (int e = 0; e < 3; e++) E.xpos()[mybody][e] = pb[e];
+            if (bip_out) {      // biped mode, last substep: data.xpos / site_xpos / xmat as the reward terms will read them
+                const T wy = E.qpos[1] + pb[1], wz = E.qpos[2] + pb[2];
+                if (lane < 12 && bi == 0) bip_out[BK_HIP_Z + bk] = wz;
+                if (lane < 12 && bi == 0 && bk >= 2) bip_out[BK_REAR_HIP_Y + bk - 2] = wy;
+                if (lane < 12 && bi == 2 && bk < 2) {
+                    const T sx = bk ? cfg.foot_site[1][0] : cfg.foot_site[0][0], sy = bk ? cfg.foot_site[1][1] : cfg.foot_site[0][1],
+                            sz = bk ? cfg.foot_site[1][2] : cfg.foot_site[0][2];
+                    bip_out[BK_FRONT_CALF_Z + bk] = wz;
+                    bip_out[BK_FRONT_FOOT_Z + bk] = wz + Rb[6] * sx + Rb[7] * sy + Rb[8] * sz;
+                }
+                if (lane == 12) bip_out[BK_TRUNK_XZ] = R0[6];
+            }
             const T dif[3] = {xip[0] - com[0], xip[1] - com[1], xip[2] - com[2]};
             cinert_of(cin, Rb, Ib, mass, dif);
 #pragma unroll

@@ -15,6 +15,7 @@
 #define GO1_DYN_SMEM(name) extern __shared__ __align__(16) unsigned char name[]
 #define GO1_LAUNCH(kernel, grid, block, smem, stream, ...) kernel<<<grid, block, smem, stream>>>(__VA_ARGS__)
 #endif
+#include <cmath>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -43,7 +44,7 @@ typedef GO1_REAL real;
 enum {
     S_QPOS = 0, S_QVEL = 19, S_WARM = 37, S_LASTACT = 55, S_AIR = 67, S_DEV = 71, S_VDES = 74, S_EPRET = 77, S_NREAL = 78, S_STRIDE = 80
 };
-enum { I_STEP = 0, I_UNHEALTHY = 1, I_LASTCON = 2, I_RESETCNT = 3, I_BAD = 4, I_NINT = 5, I_STRIDE = 8 };
+enum { I_STEP = 0, I_UNHEALTHY = 1, I_LASTCON = 2, I_RESETCNT = 3, I_BAD = 4, I_FFT = 5 /* front feet touched (biped) */, I_NINT = 6, I_STRIDE = 8 };
 // diag layout (real, per env, [field][N])
 enum { D_QACC = 0, D_QFA = 18, D_QFC = 36, D_CFRC = 54, D_TRUNKZ = 138, D_COM = 139, D_NREAL = 142 };
 enum { DI_NCON = 0, DI_ITER = 1, DI_ITERTOT = 2, DI_OVERFLOW = 3, DI_NINT = 4 };
@@ -62,6 +63,7 @@ struct KParams {
     int reset_only;
     float* obs; float* rew; uint8_t* done; uint8_t* trunc; float* term_obs; float* info;
     T* diag; int* diag_i; T* diag_con;   // nullable
+    T* bipk; float* bip_info;      // biped mode only: [N][BK_N] kinematic snapshot, [N][GO1_BIPED_INFO_DIM] reward_info terms
     double* stats;                 // nullable: 8 doubles
     int* queue;                    // environment queue head (zeroed before every launch)
     const int* order;              // queue position -> environment (sorted by last step's solver work)
@@ -143,7 +145,15 @@ GO1_DEV void reset_env(const DevModel<T>& m, const EnvCfg<T>& cfg, WEnv<T>& E, i
     const U4 r1 = philox(seed, (unsigned)gid, (unsigned)(gid >> 32), (unsigned)resetcnt, 0x52535431u);
     if (lane < 19) {
         T q = m.key_qpos[lane];
-        if (u01(r0.x) < cfg.fallen_prob) {
+        const bool fallen = u01(r0.x) < cfg.fallen_prob;
+        if (cfg.biped && !fallen) {      // :967-972: rear-leg stance, trunk pitched -95 deg, dropped from 0.65 m
+            if (lane >= 7) q = cfg.biped_ready[lane - 7];
+            if (lane == 2) q = cfg.biped_reset_z;
+            if (lane == 3) q = cfg.biped_reset_qw;
+            if (lane == 5) q = cfg.biped_reset_qy;
+            if (lane == 4 || lane == 6) q = 0;
+        }
+        if (fallen) {
             const float lo = 3.14159265358979f / 2.1f, hi = 3.14159265358979f / 1.5f;
             const float ang = lo + (hi - lo) * u01(r0.y);
             float s, c;
@@ -180,7 +190,7 @@ GO1_DEV void reset_env(const DevModel<T>& m, const EnvCfg<T>& cfg, WEnv<T>& E, i
     }
     if (lane == 0) {
         E.ep_ret = 0;
-        E.ei[I_STEP] = 0; E.ei[I_UNHEALTHY] = 0; E.ei[I_LASTCON] = 0; E.ei[I_RESETCNT] = resetcnt;
+        E.ei[I_STEP] = 0; E.ei[I_UNHEALTHY] = 0; E.ei[I_LASTCON] = 0; E.ei[I_RESETCNT] = resetcnt; E.ei[I_FFT] = 0;
     }
     __syncwarp();
 }
@@ -274,7 +284,8 @@ __global__ void __launch_bounds__(GO1_WARPS * 32, GO1_MINBLOCKS) k_step(const KP
             }
             for (int s = 0; s < cfg.frame_skip; s++) {
                 const bool last = s == cfg.frame_skip - 1;
-                substep_w(m, cfg, E, lane, out, capture && last, con_out, !out.bad);
+                substep_w(m, cfg, E, lane, out, capture && last, con_out, !out.bad,
+                          (cfg.biped && last) ? P.bipk + (size_t)env * BK_N : (T*)nullptr);
             }
             if (out.bad) { out.qacc = 0; out.qfa = 0; out.qfc = 0; out.trunk_z = 0; }
             const bool legdof = lane >= 6 && lane < NDOF;
@@ -300,13 +311,15 @@ __global__ void __launch_bounds__(GO1_WARPS * 32, GO1_MINBLOCKS) k_step(const KP
             else { lin_r = exp((double)(-(ex * ex + ey * ey) / cfg.sigma)) * rw[0]; ang_r = exp((double)(-(ez * ez) / cfg.sigma)) * rw[1]; }
             const T healthy_r = ok ? rw[2] : T(0);
             // feet air time (:633-668): lanes 0..3 = feet (calf bodies 3, 6, 9, 12)
-            T air_l = 0;
+            T air_l = 0, fmag = 0;
             int curr = 0;
             const int lastcon = E.ei[I_LASTCON];
             if (lane < 4) {
                 const T* w = E.cfrc[3 + 3 * lane];
-                const T fmag = NN::sqrt_(dot6(w, w));
+                fmag = NN::sqrt_(dot6(w, w));
                 curr = fmag > T(1);
+            }
+            if (lane < 4 && !cfg.biped) {
                 const int filt = curr | ((lastcon >> lane) & 1);
                 T air = E.air[lane];
                 const T first = (air > 0 && filt) ? T(1) : T(0);
@@ -319,6 +332,7 @@ __global__ void __launch_bounds__(GO1_WARPS * 32, GO1_MINBLOCKS) k_step(const KP
             const int newcon = (int)(__ballot_sync(FULL, curr) & 0xFu);
             T air_r = warp_sum(air_l);
             if (!(NN::sqrt_(E.vdes[0] * E.vdes[0] + E.vdes[1] * E.vdes[1]) > T(0.1))) air_r = 0;
+            if (cfg.biped) air_r = (((newcon >> 2) ^ (newcon >> 3)) & 1) ? T(1) : T(0);     // :646-649: rear feet alternate; no bookkeeping
             air_r *= rw[3];
             // recovery (:534-580)
             T dev[3] = {0, 0, 0};
@@ -335,7 +349,7 @@ __global__ void __launch_bounds__(GO1_WARPS * 32, GO1_MINBLOCKS) k_step(const KP
                 gu = hr * T(1.5) + (T(1) - (pg[0] * pg[0] + pg[1] * pg[1])) * T(0.5);
             }
             const T gu_r = gu * rw[5];
-            const T rewards = lin_r + ang_r + healthy_r + air_r + rec_r + gu_r;
+            T rewards = lin_r + ang_r + healthy_r + air_r + rec_r + gu_r;
             // costs: per-joint terms on the dof lanes, reduced across the warp
             T s_tau = 0, s_rate = 0, s_jl = 0, s_jv = 0, s_acc = 0, s_djp = 0, s_coll = 0;
             const T act_j = __shfl_sync(FULL, act, jl);      // action of this lane's joint
@@ -370,7 +384,45 @@ __global__ void __launch_bounds__(GO1_WARPS * 32, GO1_MINBLOCKS) k_step(const KP
             const T coll_c = (NN::sqrt_(s_coll) > T(0.1) ? T(1) : T(0)) * cw[8];
             const T djp_c = s_djp * cw[9];
             const T unh_c = (ok ? T(0) : T(1)) * cw[10];
-            const T costs = ctrl_c + rate_c + vert_c + xyang_c + jl_c + jv_c + acc_c + coll_c + unh_c + orient_c + djp_c;
+            T costs = ctrl_c + rate_c + vert_c + xyang_c + jl_c + jv_c + acc_c + coll_c + unh_c;
+            // ---- bipedal mode (:869-904): one reward and nine costs replace orientation / default_joint_position
+            T bterm[10] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+            if (cfg.biped) {
+                const T* bw = cfg.biped_w;
+                __syncwarp();
+                T bk[BK_N];
+                const T* bsrc = P.bipk + (size_t)env * BK_N;
+#pragma unroll
+                for (int i = 0; i < BK_N; i++) bk[i] = out.bad ? T(0) : bsrc[i];
+                const T s_fc = warp_sum(lane < 2 ? fmag * fmag : T(0));                                       // :426-431
+                const bool rear_air = (__ballot_sync(FULL, lane >= 2 && lane < 4 && fmag < T(1)) & 0xCu) == 0xCu;   // :880-882
+                T s_uc = 0, s_ab = 0;
+                for (int i = lane; i < 42; i += 32) {       // trunk, the four thighs, the front calves (:192-200, :772-781)
+                    const int k = i / 6;
+                    const int b = k == 0 ? 0 : (k <= 4 ? 2 + 3 * (k - 1) : 3 + 3 * (k - 5));
+                    const T v = E.cfrc[b][i - 6 * k];
+                    s_uc += v * v;
+                }
+                if (lane < 4) { const T qa = E.qpos[7 + 3 * lane]; s_ab = qa * qa; }                           // :759-769
+                s_uc = warp_sum(s_uc); s_ab = warp_sum(s_ab);
+                auto pos = [](T v) { return v > 0 ? v : T(0); };
+                bterm[0] = pos(bk[BK_TRUNK_XZ]) * bw[0];                                                        // :388-401
+                bterm[1] = s_fc * bw[1];
+                bterm[2] = rear_air ? bw[2] : T(0);
+                bterm[3] = (pos(bk[BK_FRONT_CALF_Z] - bk[BK_FRONT_FOOT_Z]) + pos(bk[BK_FRONT_CALF_Z + 1] - bk[BK_FRONT_FOOT_Z + 1])) * bw[3];   // :403-423
+                bterm[4] = pos(bk[BK_REAR_HIP_Y] - bk[BK_REAR_HIP_Y + 1]) * bw[4];                              // :315-331
+                bterm[5] = (pos(T(0.2) - bk[BK_HIP_Z + 2]) + pos(T(0.2) - bk[BK_HIP_Z + 3])) * T(10) * bw[5];   // :334-351
+                const T d0 = pos(bk[BK_HIP_Z] - bk[BK_FRONT_FOOT_Z]), d1 = pos(bk[BK_HIP_Z + 1] - bk[BK_FRONT_FOOT_Z + 1]);
+                bterm[6] = (d0 * d0 + d1 * d1) * bw[6];                                                         // :354-376
+                bterm[7] = s_ab * bw[7];
+                bterm[8] = s_uc * bw[8];
+                bterm[9] = T(0) * bw[9];      // :269-312 counts robot-robot contacts, which are not generated
+                rewards += bterm[0];
+#pragma unroll
+                for (int i = 1; i < 10; i++) costs += bterm[i];
+            } else {
+                costs = costs + orient_c + djp_c;
+            }
             T reward = rewards - costs;
             reward = reward > 0 ? reward : T(0);
             if (nonfinite) reward = 0;
@@ -384,7 +436,8 @@ __global__ void __launch_bounds__(GO1_WARPS * 32, GO1_MINBLOCKS) k_step(const KP
             const float x_pos = (float)E.qpos[0], y_pos = (float)E.qpos[1];
             __syncwarp();
             if (lane == 0) {
-                E.ei[I_UNHEALTHY] = unhealthy; E.ei[I_LASTCON] = newcon; E.ep_ret = ep_ret;
+                E.ei[I_UNHEALTHY] = unhealthy; E.ep_ret = ep_ret;
+                if (!cfg.biped) E.ei[I_LASTCON] = newcon;
                 if (ok) { E.dev[0] = E.dev[1] = E.dev[2] = 0; } else { E.dev[0] = dev[0]; E.dev[1] = dev[1]; E.dev[2] = dev[2]; }
             }
             // ---- optional capture of mjData (tests)
@@ -421,6 +474,18 @@ __global__ void __launch_bounds__(GO1_WARPS * 32, GO1_MINBLOCKS) k_step(const KP
                     inf[5] = (float)rec_r; inf[6] = (float)gu_r; inf[7] = (float)(-unh_c); inf[8] = (float)(-orient_c); inf[9] = (float)(-djp_c);
                     inf[10] = (float)ep_ret; inf[11] = (float)ep_len; inf[12] = (float)reason; inf[13] = ok ? 1.f : 0.f;
                     inf[14] = (float)out.iters_total; inf[15] = (float)out.ncon;
+                    if (cfg.biped) inf[8] = inf[9] = 0.f;      // the two terms biped mode drops from reward_info (:905-909)
+                }
+                if (cfg.biped) {
+                    const int touched = E.ei[I_FFT];            // latched from the forces of EARLIER steps (:477-479 runs before do_simulation)
+                    float* bi = P.bip_info + (size_t)env * GO1_BIPED_INFO_DIM;
+                    bi[0] = (float)bterm[0];
+#pragma unroll
+                    for (int i = 1; i < 10; i++) bi[i] = (float)(-bterm[i]);
+                    bi[10] = (truncated && !touched) ? 1.f : 0.f;        // bipedal_success (:520-521)
+                    const int now = touched | ((newcon & 3) ? 1 : 0);
+                    bi[11] = (float)now;
+                    E.ei[I_FFT] = now;
                 }
             }
             {
@@ -510,6 +575,7 @@ struct Go1Sim {
     DevModel<real>* dmodel = nullptr;
     real* sreal = nullptr; int* sint = nullptr;
     real* diag = nullptr; int* diag_i = nullptr; real* diag_con = nullptr;
+    real* bipk = nullptr; float* bip_info = nullptr; real* bip_ready = nullptr;      // biped mode only
     bool diag_enabled = false;
     double* stats = nullptr;
     int* queue = nullptr;
@@ -549,6 +615,10 @@ void go1_default_config(Go1EnvConfig* c) {
     c->healthy_roll[0] = -1.3962634015954636f; c->healthy_roll[1] = 1.3962634015954636f;
     c->healthy_pitch[0] = -3.14159265358979323846f; c->healthy_pitch[1] = 0.0f;
     c->tracking_sigma = 0.25f; c->obs_clip = 100.0f; c->solver_tolerance = -1.0f; c->solver_iterations = 0;
+    const float bw[10] = {15.0f, 50.0f, 5.0f, 8.0f, 5.0f, 9.0f, 6.0f, 0.7f, 150.0f, 25.0f};
+    const float ready[12] = {0.0f, 4.0f, -2.0f, 0.0f, 4.0f, -2.0f, 0.0f, 2.8f, -1.2f, 0.0f, 2.8f, -1.2f};
+    std::memcpy(c->biped_w, bw, sizeof(bw)); std::memcpy(c->biped_ready_joints, ready, sizeof(ready));
+    c->biped_reset_z = 0.65f; c->biped_reset_pitch_deg = -95.0f;
 }
 
 int go1_precision_bits(void) { return (int)sizeof(real) * 8; }
@@ -575,6 +645,14 @@ static void fill_cfg(EnvCfg<real>& k, const Go1EnvConfig& c, const DevModel<doub
     }
     k.sigma = (real)c.tracking_sigma; k.obs_clip = (real)c.obs_clip;
     k.tolerance = (real)(c.solver_tolerance >= 0 ? (double)c.solver_tolerance : M.tolerance);
+    k.biped = c.biped ? 1 : 0;
+    const double bwd[10] = {15.0, 50.0, 5.0, 8.0, 5.0, 9.0, 6.0, 0.7, 150.0, 25.0};
+    for (int i = 0; i < 10; i++) k.biped_w[i] = (real)(c.biped_w[i] == def.biped_w[i] ? bwd[i] : (double)c.biped_w[i]);
+    k.biped_ready = nullptr;   // device copy made by go1_create
+    k.biped_reset_z = (real)(c.biped_reset_z == def.biped_reset_z ? 0.65 : (double)c.biped_reset_z);
+    const double half = 0.5 * (double)c.biped_reset_pitch_deg * (3.14159265358979323846 / 180.0);     // np.deg2rad(-95) / 2 (:970-971)
+    k.biped_reset_qw = (real)std::cos(half); k.biped_reset_qy = (real)std::sin(half);
+    for (int f = 0; f < 2; f++) for (int e = 0; e < 3; e++) k.foot_site[f][e] = 0;
 }
 
 int go1_create(const void* model_blob, size_t nbytes, const Go1EnvConfig* cfg_in, int n_envs, int cuda_device, uint64_t seed,
@@ -583,12 +661,16 @@ int go1_create(const void* model_blob, size_t nbytes, const Go1EnvConfig* cfg_in
     *out = nullptr;
     Go1EnvConfig cfg;
     if (cfg_in) cfg = *cfg_in; else go1_default_config(&cfg);
-    if (cfg.biped) { g_create_err = "biped=1 is not implemented (DESIGN.md: next)"; return GO1_EUNSUPPORTED; }
     if (cfg.frame_skip <= 0 || cfg.max_episode_steps <= 0) { g_create_err = "bad config"; return GO1_EINVAL; }
     Go1Sim* h = new Go1Sim();
     if (!build_dev_model(model_blob, nbytes, h->hmodel, h->err)) { g_create_err = "model rejected: " + h->err; delete h; return GO1_EMODEL; }
     h->n_envs = n_envs; h->device = cuda_device; h->seed = seed; h->env_offset = env_id_offset;
     fill_cfg(h->cfg, cfg, h->hmodel);
+    if (cfg.biped) {
+        double fs[NLEG][3];
+        if (!read_foot_sites(model_blob, nbytes, fs, h->err)) { g_create_err = "model rejected: " + h->err; delete h; return GO1_EMODEL; }
+        for (int f = 0; f < 2; f++) for (int e = 0; e < 3; e++) h->cfg.foot_site[f][e] = (real)fs[f][e];
+    }
     auto fail = [&](const char* what, cudaError_t e) { g_create_err = std::string(what) + ": " + cudaGetErrorString(e); go1_destroy(h); return GO1_ECUDA; };
     cudaError_t e;
     if ((e = cudaSetDevice(cuda_device)) != cudaSuccess) return fail("cudaSetDevice", e);
@@ -608,6 +690,16 @@ int go1_create(const void* model_blob, size_t nbytes, const Go1EnvConfig* cfg_in
     ALLOC(h->d_tobs, sizeof(float) * 48 * N); ALLOC(h->d_info, sizeof(float) * GO1_INFO_DIM * N);
     ALLOC(h->d_done, N); ALLOC(h->d_trunc, N); ALLOC(h->d_mask, N);
     ALLOC(h->d_lo, sizeof(float) * 12); ALLOC(h->d_hi, sizeof(float) * 12);
+    if (cfg.biped) {
+        ALLOC(h->bipk, sizeof(real) * BK_N * N); ALLOC(h->bip_info, sizeof(float) * GO1_BIPED_INFO_DIM * N); ALLOC(h->bip_ready, sizeof(real) * 12);
+        real rdy[12];
+        for (int i = 0; i < 12; i++) rdy[i] = (real)(double)cfg.biped_ready_joints[i];     // 4.0, 2.8f ...: widened from float, |error| <= 1e-7 rad
+        const double exact[12] = {0.0, 4.0, -2.0, 0.0, 4.0, -2.0, 0.0, 2.8, -1.2, 0.0, 2.8, -1.2};
+        Go1EnvConfig def; go1_default_config(&def);
+        for (int i = 0; i < 12; i++) if (cfg.biped_ready_joints[i] == def.biped_ready_joints[i]) rdy[i] = (real)exact[i];
+        if ((e = cudaMemcpy(h->bip_ready, rdy, sizeof(rdy), cudaMemcpyHostToDevice)) != cudaSuccess) return fail("cudaMemcpy biped_ready", e);
+        h->cfg.biped_ready = h->bip_ready;
+    }
 #undef ALLOC
 #define HALLOC(p, bytes) if ((e = cudaMallocHost((void**)&(p), (bytes))) != cudaSuccess) return fail("cudaMallocHost " #p, e)
     HALLOC(h->h_act, sizeof(float) * 12 * N); HALLOC(h->h_obs, sizeof(float) * 48 * N); HALLOC(h->h_rew, sizeof(float) * N);
@@ -641,7 +733,7 @@ int go1_destroy(go1_handle h) {
     if (!h) return GO1_EINVAL;
     cudaSetDevice(h->device);
     if (h->stream) cudaStreamSynchronize(h->stream);
-    void* dev[] = {h->order, h->work, h->queue, h->dmodel, h->sreal, h->sint, h->diag, h->diag_i, h->diag_con, h->stats, h->d_act, h->d_obs, h->d_rew, h->d_tobs,
+    void* dev[] = {h->order, h->work, h->queue, h->dmodel, h->sreal, h->sint, h->diag, h->diag_i, h->diag_con, h->bipk, h->bip_info, h->bip_ready, h->stats, h->d_act, h->d_obs, h->d_rew, h->d_tobs,
                    h->d_info, h->d_done, h->d_trunc, h->d_mask, h->d_lo, h->d_hi};
     for (void* p : dev) if (p) cudaFree(p);
     void* host[] = {h->h_act, h->h_obs, h->h_rew, h->h_tobs, h->h_info, h->h_done, h->h_trunc, h->h_mask};
@@ -667,6 +759,7 @@ static KParams<real> base_params(go1_handle h) {
     P.model = h->dmodel; P.cfg = h->cfg; P.n_envs = h->n_envs; P.sreal = h->sreal; P.sint = h->sint;
     P.seed = h->seed; P.env_offset = h->env_offset; P.launch_counter = h->launch_counter; P.queue = h->queue; P.order = h->order; P.work = h->work;
     if (h->diag_enabled) { P.diag = h->diag; P.diag_i = h->diag_i; P.diag_con = h->diag_con; }
+    P.bipk = h->bipk; P.bip_info = h->bip_info;
     return P;
 }
 static int launch(go1_handle h, const KParams<real>& P, cudaStream_t s) {
@@ -830,6 +923,22 @@ static int copy_fields(go1_handle h, void* base, size_t elem, int nfields, int e
     return GO1_OK;
 }
 
+int go1_biped_info_host(go1_handle h, float* out) {
+    if (!h || !out) return GO1_EINVAL;
+    if (!h->bip_info) { h->err = "go1_biped_info_host: the simulator was not created with cfg.biped"; return GO1_EUNSUPPORTED; }
+    CK(cudaSetDevice(h->device));
+    CK(cudaStreamSynchronize(h->stream));
+    CK(cudaMemcpy(out, h->bip_info, sizeof(float) * GO1_BIPED_INFO_DIM * (size_t)h->n_envs, cudaMemcpyDeviceToHost));
+    return GO1_OK;
+}
+
+int go1_biped_info_dev(go1_handle h, const float** ptr) {
+    if (!h || !ptr) return GO1_EINVAL;
+    if (!h->bip_info) { h->err = "go1_biped_info_dev: the simulator was not created with cfg.biped"; return GO1_EUNSUPPORTED; }
+    *ptr = h->bip_info;
+    return GO1_OK;
+}
+
 int go1_set_state(go1_handle h, int env, const Go1State* s) {
     if (!h || !s || env < 0 || env >= h->n_envs) return GO1_EINVAL;
     real r[S_NREAL]; int iv[I_NINT];
@@ -841,7 +950,7 @@ int go1_set_state(go1_handle h, int env, const Go1State* s) {
     r[S_EPRET] = (real)s->episode_return;
     iv[I_STEP] = s->step; iv[I_UNHEALTHY] = s->unhealthy_steps;
     iv[I_LASTCON] = (s->last_contacts[0] ? 1 : 0) | (s->last_contacts[1] ? 2 : 0) | (s->last_contacts[2] ? 4 : 0) | (s->last_contacts[3] ? 8 : 0);
-    iv[I_RESETCNT] = s->reset_count; iv[I_BAD] = s->bad_state;
+    iv[I_RESETCNT] = s->reset_count; iv[I_BAD] = s->bad_state; iv[I_FFT] = s->front_feet_touched ? 1 : 0;
     int rc = copy_row(h, true, h->sreal, sizeof(real) * S_STRIDE, sizeof(real) * S_NREAL, env, r);
     if (rc) return rc;
     return copy_row(h, true, h->sint, sizeof(int) * I_STRIDE, sizeof(int) * I_NINT, env, iv);
@@ -861,6 +970,7 @@ int go1_get_state(go1_handle h, int env, Go1State* s) {
     for (int i = 0; i < 3; i++) { s->last_health_deviation[i] = r[S_DEV + i]; s->desired_velocity[i] = r[S_VDES + i]; }
     s->episode_return = r[S_EPRET];
     s->step = iv[I_STEP]; s->unhealthy_steps = iv[I_UNHEALTHY]; s->reset_count = iv[I_RESETCNT]; s->bad_state = iv[I_BAD];
+    s->front_feet_touched = iv[I_FFT]; s->pad_ = 0;
     return GO1_OK;
 }
 

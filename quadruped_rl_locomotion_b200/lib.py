@@ -15,6 +15,7 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 
 OBS_DIM, ACT_DIM, NQ, NV, NBODY, INFO_DIM, MAX_CONTACTS = 48, 12, 19, 18, 14, 16, 64
+BIPED_INFO_DIM = 12
 
 ACTION_RANDOM, ACTION_POLICY, ACTION_ZERO = 0, 1, 2
 
@@ -30,7 +31,8 @@ class EnvConfig(C.Structure):
         ("desired_vel_min", C.c_float * 3), ("desired_vel_max", C.c_float * 3), ("reward_w", C.c_float * 6),
         ("cost_w", C.c_float * 11), ("healthy_z", C.c_float * 2), ("healthy_roll", C.c_float * 2),
         ("healthy_pitch", C.c_float * 2), ("tracking_sigma", C.c_float), ("obs_clip", C.c_float),
-        ("solver_tolerance", C.c_float), ("solver_iterations", C.c_int32), ("reserved", C.c_int32 * 8),
+        ("solver_tolerance", C.c_float), ("solver_iterations", C.c_int32), ("biped_w", C.c_float * 10),
+        ("biped_ready_joints", C.c_float * 12), ("biped_reset_z", C.c_float), ("biped_reset_pitch_deg", C.c_float),
     ]
 
 
@@ -41,6 +43,7 @@ class State(C.Structure):
         ("last_health_deviation", C.c_double * 3), ("desired_velocity", C.c_double * 3),
         ("episode_return", C.c_double), ("last_contacts", C.c_int32 * 4), ("step", C.c_int32),
         ("unhealthy_steps", C.c_int32), ("reset_count", C.c_int32), ("bad_state", C.c_int32),
+        ("front_feet_touched", C.c_int32), ("pad_", C.c_int32),
     ]
 
 
@@ -71,7 +74,7 @@ EXPORTS = (
     "go1_default_config", "go1_precision_bits", "go1_version", "go1_create", "go1_destroy", "go1_last_error",
     "go1_num_envs", "go1_action_bounds", "go1_reset", "go1_step", "go1_step_host", "go1_reset_host", "go1_rollout", "go1_policy_act",
     "go1_last_rollout_timing", "go1_set_state", "go1_get_state", "go1_enable_diag", "go1_get_diag",
-    "go1_get_contacts", "go1_set_attr_f32", "go1_get_attr_f32",
+    "go1_get_contacts", "go1_set_attr_f32", "go1_get_attr_f32", "go1_biped_info_host", "go1_biped_info_dev",
 )
 
 
@@ -116,6 +119,8 @@ class Go1Lib:
         L.go1_get_contacts.argtypes = [vp, i32, C.POINTER(Contact), i32, C.POINTER(C.c_int)]
         L.go1_set_attr_f32.argtypes = [vp, C.c_char_p, C.c_float]
         L.go1_get_attr_f32.argtypes = [vp, C.c_char_p, C.POINTER(C.c_float)]
+        L.go1_biped_info_host.argtypes = [vp, f32p]
+        L.go1_biped_info_dev.argtypes = [vp, C.POINTER(C.c_void_p)]
         self.L = L
 
     def default_config(self) -> EnvConfig:
@@ -238,6 +243,19 @@ class Sim:
             v = getattr(s, k)
             out[k] = np.array(v[:]) if hasattr(v, "__len__") else v
         return out
+
+    def biped_info_host(self, out: np.ndarray | None = None) -> np.ndarray:
+        """[N][BIPED_INFO_DIM] extra reward_info terms of the last control step (biped mode only)."""
+        if out is None:
+            out = np.zeros((self.n_envs, BIPED_INFO_DIM), np.float32)
+        assert out.dtype == np.float32 and out.flags.c_contiguous and out.size == self.n_envs * BIPED_INFO_DIM
+        self._check(self.lib.L.go1_biped_info_host(self._h, _ptr(out)), "go1_biped_info_host")
+        return out
+
+    def biped_info_dev(self) -> int:
+        p = C.c_void_p()
+        self._check(self.lib.L.go1_biped_info_dev(self._h, C.byref(p)), "go1_biped_info_dev")
+        return int(p.value)
 
     def enable_diag(self, on: bool = True):
         self._check(self.lib.L.go1_enable_diag(self._h, 1 if on else 0), "go1_enable_diag")

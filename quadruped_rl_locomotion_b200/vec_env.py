@@ -63,6 +63,10 @@ except Exception:  # noqa: BLE001
 _MODEL_DIR = os.path.join(os.path.dirname(os.path.abspath(__file__)), "models")
 INFO_KEYS = ("linear_vel_tracking_reward", "reward_ctrl", "reward_survive", "recovery_reward", "get_up_reward",
              "unhealthy_state_cost", "orientation_cost", "default_joint_position_cost")
+BIPED_INFO_KEYS = ("biped_upright_reward", "biped_front_contact_cost", "biped_rear_feet_airborne_cost",
+                   "biped_front_foot_height_cost", "biped_crossed_legs_cost", "biped_low_rear_hips_cost",
+                   "biped_front_feet_below_hips_cost", "biped_abduction_joints_cost", "biped_unwanted_contact_cost",
+                   "self_collision_cost")      # go1_mujoco_env.py:893-902
 _REASONS = {0: "not_terminated", 1: "state_not_finite", 2: "unhealthy_z", 3: "unhealthy_roll", 4: "unhealthy_pitch"}
 
 
@@ -91,13 +95,12 @@ class Go1CudaVecEnv(_SB3VecEnv):
                  device: int = 0, seed: int = 0, env_id_offset: int = 0, desired_velocity_min=(-0.5, 0.0, 0.0),
                  desired_velocity_max=(0.5, 0.0, 0.0), model_dir: Optional[str] = None, precision: str = "f32",
                  library: Optional[_lib.Go1Lib] = None, full_info: bool = False):
-        if biped:
-            raise NotImplementedError("biped=True is not implemented yet (DESIGN.md, 'next'); the CUDA path refuses it")
         self._lib = library or _lib.Go1Lib(precision=precision)
         blob = load_model_blob(ctrl_type, model_dir)
         self.model = Model.from_blob(blob)
         cfg = self._lib.default_config()
         cfg.rand_power = float(rand_power)
+        cfg.biped = 1 if biped else 0           # go1_mujoco_env.py:43
         for i in range(3):
             cfg.desired_vel_min[i] = float(desired_velocity_min[i])
             cfg.desired_vel_max[i] = float(desired_velocity_max[i])
@@ -105,7 +108,7 @@ class Go1CudaVecEnv(_SB3VecEnv):
         lo, hi = self.sim.action_bounds()
         observation_space = Box(low=-np.inf, high=np.inf, shape=(_lib.OBS_DIM,), dtype=np.float64)
         action_space = Box(low=lo, high=hi, dtype=np.float32)
-        self.ctrl_type, self.biped, self._rand_power = ctrl_type, False, float(rand_power)
+        self.ctrl_type, self.biped, self._rand_power = ctrl_type, bool(biped), float(rand_power)
         self.full_info = bool(full_info)
         self.render_mode = None
         n = int(num_envs)
@@ -116,6 +119,7 @@ class Go1CudaVecEnv(_SB3VecEnv):
         self._done = np.zeros(n, np.uint8)
         self._trunc = np.zeros(n, np.uint8)
         self._info = np.zeros((n, _lib.INFO_DIM), np.float32)
+        self._binfo = np.zeros((n, _lib.BIPED_INFO_DIM), np.float32) if biped else None
         self._t_start = time.time()
         self._empty_infos = [dict() for _ in range(n)]
         if _HAVE_SB3:
@@ -142,6 +146,8 @@ class Go1CudaVecEnv(_SB3VecEnv):
     def step_wait(self):
         self.sim.step_host(self._actions, self._obs, self._rew, self._done, self._trunc, self._tobs, self._info)
         dones = self._done.astype(bool)
+        if self.biped and (self.full_info or dones.any()):
+            self.sim.biped_info_host(self._binfo)
         infos = self._make_infos(dones)
         return self._obs.astype(np.float64), self._rew.copy(), dones, infos
 
@@ -180,8 +186,13 @@ class Go1CudaVecEnv(_SB3VecEnv):
             d["termination_reason"] = "unhealthy_state_active"
         else:
             d["termination_reason"] = "not_terminated"
-        for k, key in enumerate(INFO_KEYS):
+        for k, key in enumerate(INFO_KEYS[:6] if self.biped else INFO_KEYS):      # biped mode has no orientation / default-joint terms (:905-909)
             d[key] = float(r[2 + k])
+        if self.biped:
+            b = self._binfo[i]
+            for k, key in enumerate(BIPED_INFO_KEYS):
+                d[key] = float(b[k])
+            d["bipedal_success"] = bool(b[10] > 0.5)                               # :520-521
         return d
 
     def close(self) -> None:

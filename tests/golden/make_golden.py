@@ -67,7 +67,7 @@ def record_trace(env, actions, label):
             g[i] = c.geom2; dist[i] = c.dist; fn[i] = f[c.efc_address]
         post["ncon"].append(len(cons)); post["con_geom"].append(g); post["con_dist"].append(dist); post["con_fn"].append(fn)
         post["obs"].append(obs.copy()); post["reward"].append(reward)
-        post["info"].append(np.array([info[k] for k in INFO_KEYS], dtype=np.float64))
+        post["info"].append(np.array([info.get(k, 0.0) for k in INFO_KEYS], dtype=np.float64))   # biped mode drops two keys
         post["healthy"].append(info["termination_reason"] == "not_terminated")
         post["terminated"].append(terminated); post["truncated"].append(truncated)
         post["solver_iter"].append(d.solver_iter)

@@ -33,8 +33,9 @@ def load_trace(ctrl: str):
     return pre, post
 
 
-def load_starts(ctrl: str):
-    st = np.load(os.path.join(GOLDEN, f"starts_{ctrl}.npz"))
+def load_starts(ctrl: str, biped: bool = False):
+    """``biped=True``: tests/golden/make_golden_biped.py pairs (reference env with biped=True)."""
+    st = np.load(os.path.join(GOLDEN, f"starts_biped_{ctrl}.npz" if biped else f"starts_{ctrl}.npz"))
     pre = {k[4:]: st[k] for k in st.files if k.startswith("pre_")}
     post = {k[5:]: st[k] for k in st.files if k.startswith("post_")}
     for k in st.files:
@@ -43,13 +44,17 @@ def load_starts(ctrl: str):
     return pre, post
 
 
-def run_teacher_forced(lib, ctrl: str, pre, post, idx, capture_contacts: bool = False):
+def run_teacher_forced(lib, ctrl: str, pre, post, idx, capture_contacts: bool = False, biped: bool = False):
     """Loads golden state idx[i] into env i, steps all envs ONCE with the golden actions; returns results."""
     idx = np.asarray(idx)
     n = len(idx)
-    sim = Sim(model_blob(ctrl), n, lib=lib, seed=7)
+    cfg = lib.default_config()
+    cfg.biped = 1 if biped else 0
+    sim = Sim(model_blob(ctrl), n, lib=lib, cfg=cfg, seed=7)
     sim.enable_diag(True)
     for e, t in enumerate(idx):
+        if biped:
+            sim.set_state(e, front_feet_touched=int(pre["fft"][t]))
         sim.set_state(
             e, qpos=pre["qpos"][t], qvel=pre["qvel"][t], qacc_warmstart=pre["warm"][t],
             last_action=pre["ep_last_action"][t], feet_air_time=pre["ep_feet_air_time"][t],
@@ -62,6 +67,8 @@ def run_teacher_forced(lib, ctrl: str, pre, post, idx, capture_contacts: bool = 
     tobs = np.zeros((n, 48), np.float32); info = np.zeros((n, 16), np.float32)
     sim.step_host(actions, obs, rew, done, trunc, tobs, info)
     out = dict(obs=obs, rew=rew, done=done, trunc=trunc, tobs=tobs, info=info, state=[], diag=[], contacts=[])
+    if biped:
+        out["binfo"] = sim.biped_info_host()
     for e in range(n):
         # a done env was auto-reset: its physics state is the reset state; parity on state is skipped for it
         out["state"].append(sim.get_state(e))
@@ -108,6 +115,22 @@ def compare(out, pre, post, idx):
         w["info"] = max(w["info"], float(np.abs(out["info"][e, 2:10] - post["info"][t]).max() /
                                          max(1.0, np.abs(post["info"][t]).max())))
     return w, mism
+
+
+def compare_biped(out, post, idx):
+    """Worst error of the ten biped reward_info terms (relative to max(1, |term|)) + mismatches of the two flags.
+    ``out['binfo'][:, 11]`` is the latch INCLUDING this step's front-foot forces (golden ``post_fft``)."""
+    idx = np.asarray(idx)
+    worst = np.zeros(10); flags = dict(bipedal_success=0, front_feet_touched=0)
+    for e, t in enumerate(idx):
+        g = post["binfo"][t]
+        worst = np.maximum(worst, np.abs(out["binfo"][e, :10] - g) / np.maximum(1.0, np.abs(g)))
+        flags["bipedal_success"] += int(bool(out["binfo"][e, 10] > 0.5) != bool(post["bipedal_success"][t]))
+        # a front-foot force within 1e-3 of the 1 N threshold may legitimately fall on either side in fp32
+        near = np.any(np.abs(post["front_forces"][t] - 1.0) < 1e-3)
+        if not near:
+            flags["front_feet_touched"] += int(bool(out["binfo"][e, 11] > 0.5) != bool(post["fft"][t]))
+    return worst, flags
 
 
 def contact_sets_equal(contacts, post, t, tie_eps=1e-6, margin=0.001):

@@ -31,12 +31,20 @@ def test_libraries_export_all_symbols():
         assert dll.go1_precision_bits() == (32 if prec == "f32" else 64)
 
 
-def test_struct_sizes_match_header():
-    # sizes implied by the header's field lists (catches drift between go1sim.h and lib.py)
-    assert ctypes.sizeof(L.State) == 8 * (19 + 18 + 18 + 12 + 4 + 3 + 3 + 1) + 4 * 8
-    assert ctypes.sizeof(L.Diag) == 8 * (18 * 3 + 14 * 6 + 1 + 3) + 4 * 4
-    assert ctypes.sizeof(L.EnvConfig) == 4 * (4 + 2 + 3 + 3 + 6 + 11 + 2 + 2 + 2 + 3 + 1 + 8)
-    assert ctypes.sizeof(L.Stats) == 64 and ctypes.sizeof(L.Policy) == 56
+def test_struct_sizes_match_header(tmp_path):
+    """sizeof of every struct as gcc sees include/go1sim.h == the ctypes mirror in lib.py (catches drift)."""
+    import subprocess
+    src = tmp_path / "sizes.c"
+    src.write_text('#include <stdio.h>\n#include "go1sim.h"\nint main(void){printf("%zu %zu %zu %zu %zu %zu %d %d\\n",'
+                   'sizeof(Go1State),sizeof(Go1Diag),sizeof(Go1EnvConfig),sizeof(Go1Stats),sizeof(Go1Policy),sizeof(Go1Contact),'
+                   'GO1_INFO_DIM,GO1_BIPED_INFO_DIM);return 0;}\n')
+    exe = tmp_path / "sizes"
+    subprocess.check_call(["gcc", "-I", os.path.join(ROOT, "include"), "-o", str(exe), str(src)])
+    got = [int(x) for x in subprocess.check_output([str(exe)]).split()]
+    assert got == [ctypes.sizeof(L.State), ctypes.sizeof(L.Diag), ctypes.sizeof(L.EnvConfig), ctypes.sizeof(L.Stats),
+                   ctypes.sizeof(L.Policy), ctypes.sizeof(L.Contact), L.INFO_DIM, L.BIPED_INFO_DIM]
+    assert ctypes.sizeof(L.State) == 8 * (19 + 18 + 18 + 12 + 4 + 3 + 3 + 1) + 4 * 10
+    assert ctypes.sizeof(L.EnvConfig) == 4 * (4 + 2 + 3 + 3 + 6 + 11 + 2 + 2 + 2 + 3 + 1 + 10 + 12 + 2)
 
 
 def test_missing_library_fails_loudly(tmp_path):
@@ -51,7 +59,7 @@ def test_create_rejects_garbage_without_gpu():
     import pytest
     with pytest.raises(L.Go1Error, match="model"):
         L.Sim(b"GO1MDL01" + b"\0" * 64, 4, lib=lib)
-    cfg = lib.default_config(); cfg.biped = 1
-    blob = open(os.path.join(ROOT, "quadruped_rl_locomotion_b200", "models", "go1_torque.go1m"), "rb").read()
-    with pytest.raises(L.Go1Error, match="biped"):
-        L.Sim(blob, 4, lib=lib, cfg=cfg)
+    cfg = lib.default_config()
+    assert list(cfg.biped_w) == pytest.approx([15, 50, 5, 8, 5, 9, 6, 0.7, 150, 25])          # go1_mujoco_env.py:92-101
+    assert list(cfg.biped_ready_joints) == pytest.approx([0, 4, -2, 0, 4, -2, 0, 2.8, -1.2, 0, 2.8, -1.2])   # :32-39
+    assert cfg.biped_reset_z == pytest.approx(0.65) and cfg.biped_reset_pitch_deg == -95.0

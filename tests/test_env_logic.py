@@ -98,3 +98,46 @@ def test_live_reference_env_equals_restatement():
         assert (term, trunc) == (t2, tr2)
         for k in el.INFO_KEYS:
             assert info[k] == pytest.approx(i2[k], abs=1e-10)
+
+
+def biped_kin(d):
+    """The kinematic quantities the biped terms read (go1_mujoco_env.py:322,340,360-361,379,409-410), MuJoCo body ids."""
+    ids = {"FR_hip": 2, "FR_calf": 4, "FL_hip": 5, "FL_calf": 7, "RR_hip": 8, "RL_hip": 11}
+    return dict(trunk_xaxis_z=d.xmat[1].reshape(3, 3)[2, 0],
+                front_calf_z=d.xpos[[ids["FR_calf"], ids["FL_calf"]], 2], front_feet_z=d.site_xpos[[2, 3], 2],
+                rear_hip_y=d.xpos[[ids["RR_hip"], ids["RL_hip"]], 1], rear_hip_z=d.xpos[[ids["RR_hip"], ids["RL_hip"]], 2],
+                front_hip_z=d.xpos[[ids["FR_hip"], ids["FL_hip"]], 2])
+
+
+@pytest.mark.skipif(not reference_available(), reason="reference sources not on this machine")
+@pytest.mark.parametrize("seed", [5, 6])       # seed 6 draws a fallen start
+def test_live_reference_env_biped_equals_restatement(seed):
+    """``biped=True`` (go1_mujoco_env.py:91-101, :869-904): the extra terms, the alternating-rear-feet air-time
+    reward, the front-feet-touched latch and the biped reset pose."""
+    from oracle.ref_env import make_reference_env
+    env = make_reference_env("torque", biped=True)
+    m = env.sim.model
+    assert [m.names["body"][i] for i in el.UNWANTED_CONTACT_BODIES] == ["trunk", "FR_thigh", "FL_thigh", "RR_thigh", "RL_thigh", "FR_calf", "FL_calf"]
+    assert [m.names["body"][i] for i in (2, 4, 5, 7, 8, 11)] == ["FR_hip", "FR_calf", "FL_hip", "FL_calf", "RR_hip", "RL_hip"]
+    assert list(env._front_feet_site_ids) == [2, 3]      # sites: head, imu, FR, FL, RR, RL
+    np.random.seed(seed)
+    env.reset()
+    if abs(env.data.qpos[2] - 0.1) > 1e-9:
+        assert np.allclose(env.data.qpos[7:], el.BIPEDAL_READY_JOINTS) and env.data.qpos[2] == 0.65
+    logic = el.EnvLogic(m, biped=True)
+    ep = el.EpisodeState(desired_velocity=np.array(env._desired_velocity, dtype=float))
+    rng = np.random.default_rng(9)
+    prev_ff = np.zeros(2)
+    for _ in range(40):
+        a = rng.uniform(-1, 1, 12).astype(np.float32)
+        obs, rew, term, trunc, info = env.step(a)
+        d = env.data
+        o2, r2, t2, tr2, i2 = logic.step(ep, a, d.qpos.copy(), d.qvel.copy(), d.qacc.copy(), d.qfrc_actuator.copy(),
+                                         d.cfrc_ext.copy(), d.xpos[1, 2], kin=biped_kin(d), prev_front_feet_forces=prev_ff)
+        prev_ff = np.linalg.norm(d.cfrc_ext[[4, 7]], axis=1)
+        assert np.allclose(obs, o2, atol=1e-12) and rew == pytest.approx(r2, rel=1e-9, abs=1e-9)
+        assert (term, trunc) == (t2, tr2)
+        assert env._front_feet_touched == ep.front_feet_touched
+        for k in el.BIPED_INFO_KEYS[:-1] + ("linear_vel_tracking_reward", "reward_ctrl", "get_up_reward"):
+            assert info[k] == pytest.approx(i2[k], rel=1e-9, abs=1e-9), k
+        assert info["bipedal_success"] == i2["bipedal_success"]

@@ -82,3 +82,62 @@ def test_single_substep_f32(emu_lib_f32):
         e_acc.append(pc.rel_err(d["qacc"], sub["qacc"][t])); e_pos.append(pc.rel_err(s["qpos"], nq)); e_vel.append(pc.rel_err(s["qvel"], nv))
     assert np.median(e_acc) < 2e-6 and max(e_acc) < 5e-5, (np.median(e_acc), max(e_acc))
     assert max(e_pos) < 1e-5 and max(e_vel) < 1e-5, (max(e_pos), max(e_vel))
+
+
+@pytest.mark.parametrize("ctrl", ["torque", "position"])
+def test_biped_mode_f64(emu_lib_f64, ctrl):
+    """cfg.biped = 1 against the reference's Go1MujocoEnv(biped=True): physics as before, plus the ten biped
+    reward_info terms (:869-904), the alternating-rear-feet reward (:646-649), bipedal_success (:520-521) and the
+    front-feet-touched latch (:477-479).  The fixture holds steps at the time limit with and without a touch."""
+    pre, post = pc.load_starts(ctrl, biped=True)
+    n = len(post["reward"])
+    lim = np.flatnonzero(post["truncated"])
+    idx = np.unique(np.concatenate([_sample(n, 50, seed=3), lim])).astype(int)
+    out = pc.run_teacher_forced(emu_lib_f64, ctrl, pre, post, idx, biped=True)
+    w, mism = pc.compare(out, pre, post, idx)
+    for k, tol in F64.items():
+        assert w[k] <= tol, (k, w[k])
+    assert w["obs"] <= 2e-6 and w["reward"] <= 1e-5 and w["info"] <= 1e-6
+    assert all(v == 0 for v in mism.values()), mism
+    worst, flags = pc.compare_biped(out, post, idx)
+    assert worst.max() <= 1e-6, worst          # f32 output buffer
+    assert all(v == 0 for v in flags.values()), flags
+    assert post["bipedal_success"][lim].sum() == 2 and len(lim) == 6
+
+
+def test_biped_mode_f32(emu_lib_f32):
+    pre, post = pc.load_starts("position", biped=True)
+    idx = _sample(len(post["reward"]), 40, seed=4)
+    out = pc.run_teacher_forced(emu_lib_f32, "position", pre, post, idx, biped=True)
+    w, mism = pc.compare(out, pre, post, idx)
+    for k, tol in F32.items():
+        if k != "reward":
+            assert w[k] <= tol, (k, w[k])
+    assert all(v == 0 for v in mism.values()), mism
+    worst, flags = pc.compare_biped(out, post, idx)
+    # unwanted_contact = 150 * |cfrc|^2 reaches 1e6: relative 1e-4 of the term is the cfrc_ext tolerance squared-through
+    assert worst.max() <= 2e-3, worst
+    assert all(v == 0 for v in flags.values()), flags
+
+
+def test_biped_reset_pose(emu_lib_f64):
+    """Non-fallen biped resets start from BIPEDAL_READY_JOINTS at z = 0.65 pitched -95 deg (:967-972)."""
+    from quadruped_rl_locomotion_b200.lib import Sim
+    cfg = emu_lib_f64.default_config(); cfg.biped = 1
+    sim = Sim(pc.model_blob("torque"), 24, lib=emu_lib_f64, cfg=cfg, seed=3)
+    sim.reset_host()
+    ready = np.array([0, 4.0, -2.0, 0, 4.0, -2.0, 0, 2.8, -1.2, 0, 2.8, -1.2])
+    kinds = []
+    for e in range(24):
+        s = sim.get_state(e)
+        if abs(s["qpos"][2] - 0.65) < 1e-12:
+            kinds.append("biped")
+            assert np.allclose(s["qpos"][7:], ready, atol=1e-15)
+            a = np.deg2rad(-95.0)
+            assert np.allclose(s["qpos"][3:7], [np.cos(a / 2), 0, np.sin(a / 2), 0], atol=1e-15)
+        else:
+            kinds.append("fallen")
+            assert abs(s["qpos"][2] - 0.1) < 1e-12
+        assert s["front_feet_touched"] == 0
+    assert "biped" in kinds and "fallen" in kinds
+    sim.close()

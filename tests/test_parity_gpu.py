@@ -99,3 +99,61 @@ def test_nan_injection_is_isolated(cuda_lib_f32):
     for e in range(len(idx)):
         if e != 5:
             assert np.array_equal(out["state"][e]["qpos"], ref["state"][e]["qpos"])
+
+
+@pytest.mark.parametrize("ctrl", ["torque", "position"])
+def test_biped_mode_f64(cuda_lib_f64, ctrl):
+    """cfg.biped = 1 against the reference's Go1MujocoEnv(biped=True) (tests/golden/make_golden_biped.py): every pair."""
+    pre, post = pc.load_starts(ctrl, biped=True)
+    idx = np.arange(len(post["reward"]))
+    out = pc.run_teacher_forced(cuda_lib_f64, ctrl, pre, post, idx, biped=True)
+    w, mism = pc.compare(out, pre, post, idx)
+    for k, tol in F64.items():
+        assert w[k] <= tol, (k, w[k])
+    assert w["obs"] <= 2e-6 and w["reward"] <= 1e-5 and w["info"] <= 1e-6      # f32 output buffers
+    assert all(v == 0 for v in mism.values()), mism
+    worst, flags = pc.compare_biped(out, post, idx)
+    assert worst.max() <= 1e-6, worst
+    assert all(v == 0 for v in flags.values()), flags
+
+
+@pytest.mark.parametrize("ctrl", ["torque", "position"])
+def test_biped_mode_f32(cuda_lib_f32, ctrl):
+    pre, post = pc.load_starts(ctrl, biped=True)
+    idx = np.arange(len(post["reward"]))
+    out = pc.run_teacher_forced(cuda_lib_f32, ctrl, pre, post, idx, biped=True)
+    w, mism = pc.compare(out, pre, post, idx)
+    for k, tol in F32.items():
+        if k != "reward":          # reward = max(0, 15 - 150 |cfrc|^2 ...): absolute error scales with the 1e6-sized cost terms
+            assert w[k] <= tol, (k, w[k])
+    assert all(v == 0 for v in mism.values()), mism
+    worst, flags = pc.compare_biped(out, post, idx)
+    print(ctrl, "biped terms worst rel", worst)
+    assert worst.max() <= 5e-3, worst      # unwanted_contact = 150 |cfrc_ext|^2: twice the cfrc_ext tolerance
+    assert all(v == 0 for v in flags.values()), flags
+    ok = post["reward"][idx] > 0
+    if ok.any():
+        assert np.abs(out["rew"][ok] - post["reward"][idx][ok]).max() <= 1e-3
+
+
+def test_biped_rollout_statistics(cuda_lib_f32):
+    """4096 biped environments, zero actions for 30 control steps: every non-fallen env starts from the -95 deg
+    rear-leg stance, falls from 0.65 m and the upright term decays; no bad states, terms stay finite."""
+    from quadruped_rl_locomotion_b200.lib import Sim
+    n = 4096
+    cfg = cuda_lib_f32.default_config(); cfg.biped = 1
+    sim = Sim(pc.model_blob("position"), n, lib=cuda_lib_f32, cfg=cfg, seed=5)
+    obs0 = sim.reset_host()
+    z0 = np.array([sim.get_state(e)["qpos"][2] for e in range(0, n, 64)])
+    assert set(np.round(z0, 3)) <= {0.65, 0.1}
+    act = np.tile(np.array([0, 2.8, -1.2] * 4, np.float32), (n, 1))
+    obs = np.zeros((n, 48), np.float32); rew = np.zeros(n, np.float32); done = np.zeros(n, np.uint8); trunc = np.zeros(n, np.uint8)
+    ups = []
+    for _ in range(30):
+        sim.step_host(act, obs, rew, done, trunc)
+        b = sim.biped_info_host()
+        assert np.isfinite(b).all() and np.all(b[:, 0] >= 0) and np.all(b[:, 0] <= 15.0 + 1e-4) and np.all(b[:, 1:10] <= 0)
+        ups.append(b[:, 0].mean())
+    assert ups[0] > 10.0            # 80 % of the slab starts with the trunk x-axis 5 deg from vertical
+    assert not done.any() and np.isfinite(obs).all()
+    sim.close()

@@ -90,9 +90,31 @@ def test_auto_reset_emu(emu_lib_f32):
     env.close()
 
 
-def test_biped_refused(emu_lib_f32):
-    with pytest.raises(NotImplementedError):
-        Go1CudaVecEnv(2, biped=True, library=emu_lib_f32)
+def test_biped_vec_env_emu(emu_lib_f32):
+    """Go1MujocoEnv(biped=True) through the VecEnv: the biped reward_info keys replace orientation / default joint
+    position (go1_mujoco_env.py:893-909); bipedal_success is reported on a time-limit truncation without an earlier
+    front-foot touch (:520-521) and not after one."""
+    from quadruped_rl_locomotion_b200.vec_env import BIPED_INFO_KEYS
+    n = 4
+    env = Go1CudaVecEnv(n, biped=True, library=emu_lib_f32, seed=3, full_info=True)
+    assert env.get_attr("biped") == [True] * n
+    env.reset()
+    sim = env.sim
+    sim.set_state(1, step=5999, front_feet_touched=0)
+    sim.set_state(2, step=5999, front_feet_touched=1)
+    obs, rew, dones, infos = env.step(np.zeros((n, 12), np.float32))
+    assert dones[1] and dones[2] and infos[1]["TimeLimit.truncated"] and infos[2]["TimeLimit.truncated"]
+    assert infos[1]["bipedal_success"] is True and infos[2]["bipedal_success"] is False and infos[0]["bipedal_success"] is False
+    for k in BIPED_INFO_KEYS:
+        assert k in infos[0], k
+    assert "orientation_cost" not in infos[0] and "default_joint_position_cost" not in infos[0]
+    assert 0.0 <= infos[0]["biped_upright_reward"] <= 15.0 and infos[0]["self_collision_cost"] == 0.0
+    assert sim.get_state(1)["front_feet_touched"] == 0 and sim.get_state(1)["step"] == 0      # auto-reset clears the latch
+    env.close()
+    env = Go1CudaVecEnv(2, library=emu_lib_f32)
+    with pytest.raises(Exception, match="biped"):
+        env.sim.biped_info_host()
+    env.close()
 
 
 def test_reset_distribution_emu(emu_lib_f32):

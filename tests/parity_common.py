@@ -117,6 +117,26 @@ def compare(out, pre, post, idx):
     return w, mism
 
 
+MAX_CONTACTS_PER_ENV = 40     # GO1_CW: contacts kept per environment; more are dropped and COUNTED (Go1Diag.contact_overflow)
+
+
+def drop_overflowed(out, idx, max_dropped=2):
+    """Removes the environments in which a substep had more than GO1_CW contacts (reported by the kernel itself).
+    The biped fixture holds two consecutive synthetic states (rear-leg stance joints with the trunk laid on its side
+    10 cm above the floor: 42 contacts) beyond that documented capacity; nothing else may be dropped."""
+    idx = np.asarray(idx)
+    keep = np.array([d["contact_overflow"] == 0 for d in out["diag"]])
+    assert (~keep).sum() <= max_dropped, idx[~keep]
+    sel = np.flatnonzero(keep)
+    res = {}
+    for k, v in out.items():
+        if isinstance(v, list):
+            res[k] = [v[i] for i in sel] if len(v) == len(keep) else v
+        else:
+            res[k] = v[sel]
+    return res, idx[sel]
+
+
 def compare_biped(out, post, idx):
     """Worst error of the ten biped reward_info terms (relative to max(1, |term|)) + mismatches of the two flags.
     ``out['binfo'][:, 11]`` is the latch INCLUDING this step's front-foot forces (golden ``post_fft``)."""

@@ -92,8 +92,9 @@ def test_biped_mode_f64(emu_lib_f64, ctrl):
     pre, post = pc.load_starts(ctrl, biped=True)
     n = len(post["reward"])
     lim = np.flatnonzero(post["truncated"])
-    idx = np.unique(np.concatenate([_sample(n, 50, seed=3), lim])).astype(int)
+    idx = np.unique(np.concatenate([_sample(n, 50, seed=3), lim, [182, 183]])).astype(int)
     out = pc.run_teacher_forced(emu_lib_f64, ctrl, pre, post, idx, biped=True)
+    out, idx = pc.drop_overflowed(out, idx)
     w, mism = pc.compare(out, pre, post, idx)
     for k, tol in F64.items():
         assert w[k] <= tol, (k, w[k])
@@ -102,13 +103,14 @@ def test_biped_mode_f64(emu_lib_f64, ctrl):
     worst, flags = pc.compare_biped(out, post, idx)
     assert worst.max() <= 1e-6, worst          # f32 output buffer
     assert all(v == 0 for v in flags.values()), flags
-    assert post["bipedal_success"][lim].sum() == 2 and len(lim) == 6
+    assert post["bipedal_success"][lim].sum() == 2 and len(lim) == 6 and set(lim) <= set(idx)
 
 
 def test_biped_mode_f32(emu_lib_f32):
     pre, post = pc.load_starts("position", biped=True)
     idx = _sample(len(post["reward"]), 40, seed=4)
     out = pc.run_teacher_forced(emu_lib_f32, "position", pre, post, idx, biped=True)
+    out, idx = pc.drop_overflowed(out, idx)
     w, mism = pc.compare(out, pre, post, idx)
     for k, tol in F32.items():
         if k != "reward":
@@ -141,3 +143,14 @@ def test_biped_reset_pose(emu_lib_f64):
         assert s["front_feet_touched"] == 0
     assert "biped" in kinds and "fallen" in kinds
     sim.close()
+
+
+def test_contact_overflow_is_counted(emu_lib_f64):
+    """More than GO1_CW = 40 simultaneous contacts: the extra ones (geom order) are dropped, and the drop is reported."""
+    pre, post = pc.load_starts("torque", biped=True)
+    over = np.flatnonzero(post["ncon"] > pc.MAX_CONTACTS_PER_ENV)
+    assert len(over) >= 1
+    out = pc.run_teacher_forced(emu_lib_f64, "torque", pre, post, over[:2], biped=True)
+    for e in range(len(over[:2])):
+        assert out["diag"][e]["contact_overflow"] > 0 and out["diag"][e]["ncon"] == pc.MAX_CONTACTS_PER_ENV
+        assert np.isfinite(out["state"][e]["qpos"]).all()

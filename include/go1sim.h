@@ -195,7 +195,9 @@ int go1_policy_act(go1_handle h, const Go1Policy* policy, const float* obs_dev, 
  * biped_rear_feet_airborne_cost, biped_front_foot_height_cost, biped_crossed_legs_cost, biped_low_rear_hips_cost,
  * biped_front_feet_below_hips_cost, biped_abduction_joints_cost, biped_unwanted_contact_cost, self_collision_cost
  * (go1_mujoco_env.py:893-902, costs negated as there), bipedal_success (:520-521), front_feet_touched (:477-479).
- * go1_biped_info_dev returns the device pointer of the same rows for device-resident callers. */
+ * go1_biped_info_dev returns the device pointer of the same rows for device-resident callers.
+ * go1_biped_info_host synchronises the handle's own stream (go1_step_host, go1_rollout with stream NULL); after
+ * go1_step on a caller-owned stream, synchronise that stream first. */
 int go1_biped_info_host(go1_handle h, float* out);
 int go1_biped_info_dev(go1_handle h, const float** ptr);
 

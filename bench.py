@@ -165,7 +165,9 @@ def run_ours(args, rank, world, local):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     n = args.envs_per_gpu
     lib = Go1Lib()
-    sim = Sim(load_model_blob(args.ctrl), n, lib=lib, device=local, seed=1234, env_id_offset=rank * n)
+    cfg = lib.default_config()
+    cfg.biped = 1 if args.biped else 0      # go1_mujoco_env.py:43 (train.py --biped); default off = BASELINE's configs
+    sim = Sim(load_model_blob(args.ctrl), n, lib=lib, cfg=cfg, device=local, seed=1234, env_id_offset=rank * n)
     policy = None
     mode = ACTION_RANDOM
     keep = []
@@ -210,7 +212,7 @@ def run_ours(args, rank, world, local):
 
     # ---- e2e through the public API: host actions -> VecEnv.step -> host obs/reward/done
     sim.close()
-    env = Go1CudaVecEnv(n, ctrl_type=args.ctrl, device=local, seed=1234, env_id_offset=rank * n, library=lib)
+    env = Go1CudaVecEnv(n, ctrl_type=args.ctrl, biped=bool(args.biped), device=local, seed=1234, env_id_offset=rank * n, library=lib)
     env.reset()
     lo, hi = env.action_space.low, env.action_space.high
     rng = np.random.default_rng(rank)
@@ -243,7 +245,7 @@ def run_ours(args, rank, world, local):
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": per_launch_ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic",
-            "config": {"workload": f"Go1 {args.ctrl} control, {n} envs/GPU, {args.actions} actions, frame_skip 10, fused obs/reward/auto-reset",
+            "config": {"workload": f"Go1 {args.ctrl} control{' (biped mode)' if args.biped else ''}, {n} envs/GPU, {args.actions} actions, frame_skip 10, fused obs/reward/auto-reset",
                        "envs_per_gpu": n, "parallelism": f"env-slab x{world} (no data-path collective)",
                        "l2": "flushed between timed steps (256 MiB write, untimed)", "timing": "CUDA events on the launch stream, max over ranks"},
             "roofline": {"bound": "hbm", "achieved": ach_gbs, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": ach_gbs / peaks["hbm_gbs"],
@@ -275,6 +277,7 @@ def main():
     ap.add_argument("--envs-per-gpu", type=int, default=ENVS_PER_GPU)
     ap.add_argument("--ctrl", default="torque", choices=["torque", "position"])
     ap.add_argument("--actions", default="random", choices=["random", "policy"])
+    ap.add_argument("--biped", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     rank, world, local = _dist_env()

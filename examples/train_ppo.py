@@ -72,6 +72,7 @@ def main(argv=None):
     ap.add_argument("--seed", type=int, default=0)
     ap.add_argument("--fixed_velocity", type=float, default=0.5)           # the "x=1" target (scaled obs slot = 1)
     ap.add_argument("--save", default=None)
+    ap.add_argument("--biped", action="store_true")                          # train.py:192-196
     args = ap.parse_args(argv)
 
     rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1")); local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -84,6 +85,7 @@ def main(argv=None):
     lib = Go1Lib()
     cfg = lib.default_config()
     cfg.rand_power = args.rand_power
+    cfg.biped = 1 if args.biped else 0
     cfg.desired_vel_min[0] = cfg.desired_vel_max[0] = args.fixed_velocity
     sim = Sim(load_model_blob(args.ctrl_type), n, lib=lib, cfg=cfg, device=local, seed=args.seed, env_id_offset=rank * n)
     lo, hi = (torch.from_numpy(x).to(dev) for x in sim.action_bounds())

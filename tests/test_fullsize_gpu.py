@@ -112,3 +112,22 @@ def test_sampled_envs_follow_the_oracle(cuda_lib_f32):
         worst = max(worst, float(np.abs(s["qpos"] - o.data.qpos).max()))
     assert worst < 1e-4, worst
     sim.close()
+
+
+@pytest.mark.parametrize("n", [1, 13, 3553])
+def test_ragged_slab_sizes(cuda_lib_f32, n):
+    """Slab sizes that are not a multiple of the 12 environments a block pulls from the queue (1 env, one env more
+    than a block, one env more than a full wave of 296 blocks): env k equals env k of a 16-env slab, bit for bit."""
+    blob = pc.model_blob("torque")
+    a = Sim(blob, n, lib=cuda_lib_f32, seed=9); b = Sim(blob, 16, lib=cuda_lib_f32, seed=9)
+    for s in (a, b):
+        s.reset_host()
+        for _ in range(5):
+            st = s.rollout(1, ACTION_RANDOM, None)
+        assert st["env_steps"] == s.n_envs and st["n_bad_state"] == 0
+    for e in range(min(n, 16)):
+        sa, sb = a.get_state(e), b.get_state(e)
+        assert np.array_equal(sa["qpos"], sb["qpos"]) and np.array_equal(sa["qvel"], sb["qvel"]) and sa["step"] == 5
+    last = a.get_state(n - 1)
+    assert last["step"] == 5 and np.isfinite(last["qpos"]).all() and abs(np.linalg.norm(last["qpos"][3:7]) - 1) < 1e-5
+    a.close(); b.close()

@@ -177,6 +177,12 @@ int go1_step(go1_handle h, const float* actions_dev, float* obs_dev, float* rew_
 int go1_step_host(go1_handle h, const float* actions, float* obs, float* rew, uint8_t* done, uint8_t* trunc,
                   float* terminal_obs, float* info);
 int go1_reset_host(go1_handle h, const uint8_t* mask, float* obs);
+/* Optional: page-lock a caller-owned host buffer (cudaHostRegister).  go1_step_host copies to / from buffers that lie
+ * inside a registered range directly (no staging through the library's own pinned buffers).  What SubprocVecEnv's
+ * pipes + np.stack were in the reference (SB3 subproc_vec_env.py step_wait) becomes one DMA per array.
+ * Unregister before freeing the memory; go1_destroy unregisters what is left. */
+int go1_host_register(go1_handle h, void* ptr, size_t bytes);
+int go1_host_unregister(go1_handle h, void* ptr);
 
 /* device-resident stepping loop (throughput path): n_steps control steps with actions produced on the
  * device; accumulates stats on the device and copies them to *out (nullable) at the end (synchronous). */

@@ -590,6 +590,7 @@ struct Go1Sim {
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     unsigned long long seed = 0, env_offset = 0, launch_counter = 0;
     float last_ms = 0; int last_launches = 0;
+    std::vector<std::pair<char*, size_t>> pinned;     // caller buffers page-locked through go1_host_register
     std::string err;
 };
 
@@ -736,6 +737,8 @@ int go1_destroy(go1_handle h) {
     void* dev[] = {h->order, h->work, h->queue, h->dmodel, h->sreal, h->sint, h->diag, h->diag_i, h->diag_con, h->bipk, h->bip_info, h->bip_ready, h->stats, h->d_act, h->d_obs, h->d_rew, h->d_tobs,
                    h->d_info, h->d_done, h->d_trunc, h->d_mask, h->d_lo, h->d_hi};
     for (void* p : dev) if (p) cudaFree(p);
+    for (auto& r : h->pinned) cudaHostUnregister(r.first);
+    h->pinned.clear();
     void* host[] = {h->h_act, h->h_obs, h->h_rew, h->h_tobs, h->h_info, h->h_done, h->h_trunc, h->h_mask};
     for (void* p : host) if (p) cudaFreeHost(p);
     if (h->ev0) cudaEventDestroy(h->ev0);
@@ -797,25 +800,66 @@ int go1_step(go1_handle h, const float* actions_dev, float* obs_dev, float* rew_
     return launch(h, P, stream ? (cudaStream_t)stream : h->stream);
 }
 
+// true when [p, p + bytes) lies inside a buffer the caller page-locked with go1_host_register: DMA goes straight to it
+static bool caller_pinned(go1_handle h, const void* p, size_t bytes) {
+    const char* c = (const char*)p;
+    for (const auto& r : h->pinned)
+        if (c >= r.first && c + bytes <= r.first + r.second) return true;
+    return false;
+}
+
+int go1_host_register(go1_handle h, void* ptr, size_t bytes) {
+    if (!h || !ptr || !bytes) return GO1_EINVAL;
+    CK(cudaSetDevice(h->device));
+    CK(cudaHostRegister(ptr, bytes, cudaHostRegisterDefault));
+    h->pinned.emplace_back((char*)ptr, bytes);
+    return GO1_OK;
+}
+
+int go1_host_unregister(go1_handle h, void* ptr) {
+    if (!h || !ptr) return GO1_EINVAL;
+    for (size_t i = 0; i < h->pinned.size(); i++)
+        if (h->pinned[i].first == (char*)ptr) {
+            CK(cudaSetDevice(h->device));
+            if (h->stream) CK(cudaStreamSynchronize(h->stream));
+            h->pinned.erase(h->pinned.begin() + i);
+            CK(cudaHostUnregister(ptr));
+            return GO1_OK;
+        }
+    h->err = "go1_host_unregister: pointer was not registered";
+    return GO1_EINVAL;
+}
+
 int go1_step_host(go1_handle h, const float* actions, float* obs, float* rew, uint8_t* done, uint8_t* trunc, float* terminal_obs, float* info) {
     if (!h || !actions || !obs || !rew || !done || !trunc) { if (h) h->err = "go1_step_host: null buffer"; return GO1_EINVAL; }
     CK(cudaSetDevice(h->device));
     const size_t N = (size_t)h->n_envs;
-    std::memcpy(h->h_act, actions, sizeof(float) * 12 * N);
-    CK(cudaMemcpyAsync(h->d_act, h->h_act, sizeof(float) * 12 * N, cudaMemcpyHostToDevice, h->stream));
+    const size_t b_act = sizeof(float) * 12 * N, b_obs = sizeof(float) * 48 * N, b_rew = sizeof(float) * N, b_info = sizeof(float) * GO1_INFO_DIM * N;
+    // pageable caller buffers are staged through the library's pinned ones; registered buffers are the DMA endpoints themselves
+    const float* src_act = actions;
+    if (!caller_pinned(h, actions, b_act)) { std::memcpy(h->h_act, actions, b_act); src_act = h->h_act; }
+    float* dst_obs = caller_pinned(h, obs, b_obs) ? obs : h->h_obs;
+    float* dst_rew = caller_pinned(h, rew, b_rew) ? rew : h->h_rew;
+    uint8_t* dst_done = caller_pinned(h, done, N) ? done : h->h_done;
+    uint8_t* dst_trunc = caller_pinned(h, trunc, N) ? trunc : h->h_trunc;
+    float* dst_tobs = terminal_obs ? (caller_pinned(h, terminal_obs, b_obs) ? terminal_obs : h->h_tobs) : nullptr;
+    float* dst_info = info ? (caller_pinned(h, info, b_info) ? info : h->h_info) : nullptr;
+    CK(cudaMemcpyAsync(h->d_act, src_act, b_act, cudaMemcpyHostToDevice, h->stream));
     int rc = go1_step(h, h->d_act, h->d_obs, h->d_rew, h->d_done, h->d_trunc, h->d_tobs, info ? h->d_info : nullptr, h->stream);
     if (rc != GO1_OK) return rc;
-    CK(cudaMemcpyAsync(h->h_obs, h->d_obs, sizeof(float) * 48 * N, cudaMemcpyDeviceToHost, h->stream));
-    CK(cudaMemcpyAsync(h->h_rew, h->d_rew, sizeof(float) * N, cudaMemcpyDeviceToHost, h->stream));
-    CK(cudaMemcpyAsync(h->h_done, h->d_done, N, cudaMemcpyDeviceToHost, h->stream));
-    CK(cudaMemcpyAsync(h->h_trunc, h->d_trunc, N, cudaMemcpyDeviceToHost, h->stream));
-    if (terminal_obs) CK(cudaMemcpyAsync(h->h_tobs, h->d_tobs, sizeof(float) * 48 * N, cudaMemcpyDeviceToHost, h->stream));
-    if (info) CK(cudaMemcpyAsync(h->h_info, h->d_info, sizeof(float) * GO1_INFO_DIM * N, cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaMemcpyAsync(dst_obs, h->d_obs, b_obs, cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaMemcpyAsync(dst_rew, h->d_rew, b_rew, cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaMemcpyAsync(dst_done, h->d_done, N, cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaMemcpyAsync(dst_trunc, h->d_trunc, N, cudaMemcpyDeviceToHost, h->stream));
+    if (dst_tobs) CK(cudaMemcpyAsync(dst_tobs, h->d_tobs, b_obs, cudaMemcpyDeviceToHost, h->stream));
+    if (dst_info) CK(cudaMemcpyAsync(dst_info, h->d_info, b_info, cudaMemcpyDeviceToHost, h->stream));
     CK(cudaStreamSynchronize(h->stream));
-    std::memcpy(obs, h->h_obs, sizeof(float) * 48 * N); std::memcpy(rew, h->h_rew, sizeof(float) * N);
-    std::memcpy(done, h->h_done, N); std::memcpy(trunc, h->h_trunc, N);
-    if (terminal_obs) std::memcpy(terminal_obs, h->h_tobs, sizeof(float) * 48 * N);
-    if (info) std::memcpy(info, h->h_info, sizeof(float) * GO1_INFO_DIM * N);
+    if (dst_obs != obs) std::memcpy(obs, dst_obs, b_obs);
+    if (dst_rew != rew) std::memcpy(rew, dst_rew, b_rew);
+    if (dst_done != done) std::memcpy(done, dst_done, N);
+    if (dst_trunc != trunc) std::memcpy(trunc, dst_trunc, N);
+    if (terminal_obs && dst_tobs != terminal_obs) std::memcpy(terminal_obs, dst_tobs, b_obs);
+    if (info && dst_info != info) std::memcpy(info, dst_info, b_info);
     return GO1_OK;
 }
 

@@ -75,6 +75,7 @@ EXPORTS = (
     "go1_num_envs", "go1_action_bounds", "go1_reset", "go1_step", "go1_step_host", "go1_reset_host", "go1_rollout", "go1_policy_act",
     "go1_last_rollout_timing", "go1_set_state", "go1_get_state", "go1_enable_diag", "go1_get_diag",
     "go1_get_contacts", "go1_set_attr_f32", "go1_get_attr_f32", "go1_biped_info_host", "go1_biped_info_dev",
+    "go1_host_register", "go1_host_unregister",
 )
 
 
@@ -120,6 +121,8 @@ class Go1Lib:
         L.go1_set_attr_f32.argtypes = [vp, C.c_char_p, C.c_float]
         L.go1_get_attr_f32.argtypes = [vp, C.c_char_p, C.POINTER(C.c_float)]
         L.go1_biped_info_host.argtypes = [vp, f32p]
+        L.go1_host_register.argtypes = [vp, vp, C.c_size_t]
+        L.go1_host_unregister.argtypes = [vp, vp]
         L.go1_biped_info_dev.argtypes = [vp, C.POINTER(C.c_void_p)]
         self.L = L
 
@@ -243,6 +246,15 @@ class Sim:
             v = getattr(s, k)
             out[k] = np.array(v[:]) if hasattr(v, "__len__") else v
         return out
+
+    def host_register(self, arr: np.ndarray) -> None:
+        """Page-lock a persistent numpy buffer so ``step_host`` DMAs straight into it (keep ``arr`` alive until
+        ``host_unregister`` / ``close``)."""
+        assert arr.flags.c_contiguous
+        self._check(self.lib.L.go1_host_register(self._h, arr.ctypes.data, arr.nbytes), "go1_host_register")
+
+    def host_unregister(self, arr: np.ndarray) -> None:
+        self._check(self.lib.L.go1_host_unregister(self._h, arr.ctypes.data), "go1_host_unregister")
 
     def biped_info_host(self, out: np.ndarray | None = None) -> np.ndarray:
         """[N][BIPED_INFO_DIM] extra reward_info terms of the last control step (biped mode only)."""

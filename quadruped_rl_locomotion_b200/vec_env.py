@@ -120,6 +120,14 @@ class Go1CudaVecEnv(_SB3VecEnv):
         self._trunc = np.zeros(n, np.uint8)
         self._info = np.zeros((n, _lib.INFO_DIM), np.float32)
         self._binfo = np.zeros((n, _lib.BIPED_INFO_DIM), np.float32) if biped else None
+        # the step buffers live as long as the env: page-lock them once so every step is DMA to / from these arrays
+        self._pinned = []
+        for a in (self._actions, self._obs, self._tobs, self._rew, self._done, self._trunc, self._info):
+            try:
+                self.sim.host_register(a)
+                self._pinned.append(a)
+            except _lib.Go1Error:      # e.g. locked-memory limit: the library then stages through its own pinned buffers
+                pass
         self._t_start = time.time()
         self._empty_infos = [dict() for _ in range(n)]
         if _HAVE_SB3:
@@ -195,7 +203,19 @@ class Go1CudaVecEnv(_SB3VecEnv):
             d["bipedal_success"] = bool(b[10] > 0.5)                               # :520-521
         return d
 
+    def __del__(self):
+        try:
+            self.close()       # unregister the page-locked arrays before numpy frees them
+        except Exception:
+            pass
+
     def close(self) -> None:
+        for a in getattr(self, "_pinned", []):
+            try:
+                self.sim.host_unregister(a)
+            except _lib.Go1Error:
+                pass
+        self._pinned = []
         self.sim.close()
 
     def get_attr(self, attr_name: str, indices=None) -> List[Any]:

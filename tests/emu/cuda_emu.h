@@ -195,6 +195,7 @@ typedef int cudaError_t;
 typedef void* cudaStream_t;
 typedef void* cudaEvent_t;
 enum { cudaSuccess = 0 };
+enum { cudaHostRegisterDefault = 0 };
 enum { cudaMemcpyHostToDevice = 1, cudaMemcpyDeviceToHost = 2, cudaMemcpyDeviceToDevice = 3, cudaStreamNonBlocking = 1,
        cudaFuncAttributeMaxDynamicSharedMemorySize = 8, cudaFuncAttributePreferredSharedMemoryCarveout = 9 };
 inline const char* cudaGetErrorString(cudaError_t) { return "emu"; }
@@ -209,6 +210,8 @@ inline cudaError_t cudaEventRecord(cudaEvent_t, cudaStream_t) { return 0; }
 inline cudaError_t cudaEventElapsedTime(float* ms, cudaEvent_t, cudaEvent_t) { *ms = 0; return 0; }
 template <typename T> inline cudaError_t cudaMalloc(T** p, size_t n) { *p = (T*)std::malloc(n ? n : 1); return *p ? 0 : 2; }
 template <typename T> inline cudaError_t cudaMallocHost(T** p, size_t n) { *p = (T*)std::malloc(n ? n : 1); return *p ? 0 : 2; }
+inline cudaError_t cudaHostRegister(void*, size_t, unsigned) { return 0; }
+inline cudaError_t cudaHostUnregister(void*) { return 0; }
 inline cudaError_t cudaFree(void* p) { std::free(p); return 0; }
 inline cudaError_t cudaFreeHost(void* p) { std::free(p); return 0; }
 inline cudaError_t cudaMemset(void* p, int v, size_t n) { std::memset(p, v, n); return 0; }

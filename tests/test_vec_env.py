@@ -189,3 +189,40 @@ def test_reset_joint_noise_emu(emu_lib_f32):
     q2 = np.array([sim.get_state(e)["qpos"][7:] for e in range(n)])
     assert abs((q2 - home)[:, free].std() - 0.05) < 0.006
     sim.close()
+
+
+@pytest.mark.gpu
+def test_registered_buffers_gpu(cuda_lib_f32):
+    """Real cudaHostRegister path: VecEnv (page-locked arrays, direct DMA) == Sim.step_host on pageable arrays."""
+    _registered_vs_pageable(cuda_lib_f32, 1000)
+
+
+def test_registered_and_pageable_buffers_give_identical_steps(emu_lib_f32):
+    _registered_vs_pageable(emu_lib_f32, 5)
+
+
+def _registered_vs_pageable(emu_lib_f32, n):
+    """go1_step_host with caller buffers registered through go1_host_register (the VecEnv's own arrays) and with
+    plain pageable arrays (Sim.step_host from a test) must return the same bytes; partial overlap with a registered
+    range falls back to staging."""
+    from quadruped_rl_locomotion_b200.lib import Sim
+    env = Go1CudaVecEnv(n, library=emu_lib_f32, seed=4)
+    assert len(env._pinned) == 7
+    sim2 = Sim(pc.model_blob("torque"), n, lib=emu_lib_f32, seed=4)
+    env.reset(); sim2.reset_host()
+    rng = np.random.default_rng(0)
+    obs = np.zeros((n, 48), np.float32); rew = np.zeros(n, np.float32); done = np.zeros(n, np.uint8); trunc = np.zeros(n, np.uint8)
+    for _ in range(3):
+        a = rng.uniform(-1, 1, (n, 12)).astype(np.float32)
+        o1, r1, d1, _ = env.step(a)
+        sim2.step_host(a, obs, rew, done, trunc)
+        assert np.array_equal(o1.astype(np.float32), obs) and np.array_equal(r1, rew) and np.array_equal(d1, done.astype(bool))
+    big = np.zeros((n + 1, 48), np.float32)
+    env.sim.host_register(big)
+    env.sim.step_host(a, big[1:], rew, done, trunc)          # inside the registered range, not at its start
+    sim2.step_host(a, obs, rew, done, trunc)
+    assert np.array_equal(big[1:], obs)
+    env.sim.host_unregister(big)
+    with pytest.raises(Exception):
+        env.sim.host_unregister(big)
+    env.close(); sim2.close()

@@ -515,6 +515,10 @@ __global__ void __launch_bounds__(GO1_WARPS * 32, GO1_MINBLOCKS) k_step(const KP
 // heaviest first).  The warps of a block advance in lockstep, so a block is as slow as its slowest environment:
 // neighbours in the queue should need about the same number of Newton iterations.  Results do not depend on the order.
 __global__ void k_order(const int* __restrict__ work, int* __restrict__ order, int n) {
+#ifdef GO1_DBG_IDENTITY_ORDER      // timing experiment only: queue in slab order
+    for (int i = threadIdx.x; i < n; i += blockDim.x) order[i] = i;
+    return;
+#endif
     __shared__ int hist[256];
     for (int i = threadIdx.x; i < 256; i += blockDim.x) hist[i] = 0;
     __syncthreads();

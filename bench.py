@@ -151,7 +151,7 @@ def run_reference(args, rank, world):
         "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def run_ours(args, rank, world, local):
@@ -263,12 +263,34 @@ def run_ours(args, rank, world, local):
             "gpu_launches": launches, "clocks": clk,
             "rollout_stats": {k: stats[k] for k in ("sum_reward", "n_episodes", "n_terminated", "n_truncated", "n_bad_state", "env_steps")},
         }
-        print(json.dumps(line), flush=True)
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
 
 
+_RESULT_FD = None
+
+
+def own_stdout():
+    """stdout must carry exactly ONE JSON line, but libraries write banners to fd 1 from C (NCCL prints
+    "NCCL version ..." at communicator creation): keep a private copy of the real stdout for the result and point
+    fd 1 at stderr for everything else."""
+    global _RESULT_FD
+    sys.stdout.flush()
+    _RESULT_FD = os.dup(1)
+    os.dup2(2, 1)
+
+
+def emit(line: dict):
+    data = (json.dumps(line) + "\n").encode()
+    if _RESULT_FD is None:
+        sys.stdout.write(data.decode()); sys.stdout.flush()
+    else:
+        os.write(_RESULT_FD, data)
+
+
 def main():
+    own_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=200)

@@ -197,7 +197,7 @@ GO1_DEV void reset_env(const DevModel<T>& m, const EnvCfg<T>& cfg, WEnv<T>& E, i
 
 // ---------------------------------------------------------------------------------------------
 template <typename T>
-__global__ void __launch_bounds__(GO1_WARPS * 32, GO1_MINBLOCKS) k_step(const KParams<T> P) {
+__global__ void __launch_bounds__(GO1_WARPS * 32, GO1_MINBLOCKS) k_step(const __grid_constant__ KParams<T> P) {
     GO1_DYN_SMEM(smem_raw);
     constexpr size_t MODEL_BYTES = (sizeof(DevModel<T>) + 15) & ~size_t(15);
     DevModel<T>& m = *reinterpret_cast<DevModel<T>*>(smem_raw);

@@ -33,6 +33,7 @@
 #define __noinline__
 #define __restrict__
 #define __launch_bounds__(...)
+#define __grid_constant__
 #define __align__(x) alignas(x)
 #define __shared__ static thread_local
 

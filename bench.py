@@ -30,8 +30,8 @@ ENVS_PER_GPU = 16384
 ALG_BYTES_PER_ENV_STEP = 904.0     # 82 state words r+w, 12 action floats in, obs/reward/flags out
 ALG_FLOP_PER_ENV_STEP = 0.67e6     # SURVEY 8(d) nominal (10 substeps x (25k + 3 Newton iterations x 14k))
 # dram__bytes_read.sum + dram__bytes_write.sum of ONE k_step launch at 16384 envs, from the committed ncu --set full capture
-# (profiles/r1_ncu_k_step_warp2_raw_selected.txt): 9.05 MB + 12.08 MB
-NCU_DRAM_BYTES_PER_LAUNCH_16K = 21.13e6
+# (profiles/r1_ncu_k_step_final_raw_selected.txt): 9.96 MB + 18.08 MB
+NCU_DRAM_BYTES_PER_LAUNCH_16K = 28.05e6
 
 
 def _peaks():

@@ -110,3 +110,111 @@ def test_random_states_gpu_f32(cuda_lib_f32, ctrl):
 def test_random_states_emu_f32(emu_lib_f32):
     r = _run(emu_lib_f32, "torque", 48, seed=14, tol=F32, quantile=0.9)
     print(r)
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# the fused epilogue (obs / rewards / health / termination / episode bookkeeping, quadruped and biped mode) on random
+# physics states AND random episode states, against the numpy restatement of go1_mujoco_env.py (oracle/env_logic.py,
+# itself checked against the live reference class in tests/test_env_logic.py)
+def _run_env_logic(lib, ctrl, biped, n, seed, tol):
+    from oracle import env_logic as el
+    from oracle.oracle import OracleSim
+    blob = pc.model_blob(ctrl)
+    model = Model.from_blob(blob)
+    states = random_states(model, n, seed)
+    rng = np.random.default_rng(seed + 1000)
+    cfg = lib.default_config(); cfg.biped = 1 if biped else 0
+    sim = Sim(blob, n, lib=lib, cfg=cfg, seed=1)
+    sim.enable_diag(True)
+    eps = []
+    for e, s in enumerate(states):
+        ep = dict(last_action=rng.uniform(-1, 1, 12), feet_air_time=np.where(rng.random(4) < 0.3, 0.0, rng.uniform(0, 0.6, 4)),
+                  last_contacts=(rng.random(4) < 0.5).astype(int), last_dev=np.where(rng.random(3) < 0.5, 0.0, rng.uniform(0, 0.3, 3)),
+                  vdes=np.array([rng.uniform(-0.5, 0.5), 0.0, 0.0]), step=int(rng.choice([0, 17, 2500, 5998, 5999])),
+                  unhealthy=int(rng.choice([0, 3, 749, 750])), fft=int(rng.random() < 0.3))
+        eps.append(ep)
+        sim.set_state(e, qpos=s["qpos"], qvel=s["qvel"], qacc_warmstart=s["warm"], last_action=ep["last_action"],
+                      feet_air_time=ep["feet_air_time"], last_contacts=ep["last_contacts"], last_health_deviation=ep["last_dev"],
+                      desired_velocity=ep["vdes"], step=ep["step"], unhealthy_steps=ep["unhealthy"], front_feet_touched=ep["fft"],
+                      episode_return=0.0, bad_state=0)
+    act = np.ascontiguousarray(np.array([s["action"] for s in states], np.float32))
+    obs = np.zeros((n, 48), np.float32); rew = np.zeros(n, np.float32); done = np.zeros(n, np.uint8); trunc = np.zeros(n, np.uint8)
+    tobs = np.zeros((n, 48), np.float32); info = np.zeros((n, 16), np.float32)
+    sim.step_host(act, obs, rew, done, trunc, tobs, info)
+    binfo = sim.biped_info_host() if biped else None
+    logic = el.EnvLogic(model, biped=biped)
+    o = OracleSim(model)
+    worst = dict(obs=0.0, reward=0.0, info=0.0, binfo=0.0, air=0.0, dev=0.0)
+    flags = dict(done=0, trunc=0, healthy=0, last_contacts=0, unhealthy=0, success=0, fft=0)
+    checked = 0
+    for e, (s, p) in enumerate(zip(states, eps)):
+        if sim.get_diag(e)["contact_overflow"]:
+            continue
+        o.reset_data()
+        o.data.qpos[:] = s["qpos"]; o.data.qvel[:] = s["qvel"]; o.data.qacc_warmstart[:] = s["warm"]; o.data.ctrl[:] = act[e].astype(np.float64)
+        o.step(10); o.rne_post_constraint()
+        d = o.data
+        ep = el.EpisodeState(step=p["step"], last_action=p["last_action"].copy(), feet_air_time=p["feet_air_time"].copy(),
+                             last_contacts=p["last_contacts"].astype(bool), desired_velocity=p["vdes"].copy(),
+                             time_unhealthy=p["unhealthy"] * el.DT, last_dev=p["last_dev"].copy(), front_feet_touched=bool(p["fft"]))
+        kin = None
+        if biped:
+            kin = dict(trunk_xaxis_z=d.xmat[1].reshape(3, 3)[2, 0], front_calf_z=d.xpos[[4, 7], 2], front_feet_z=d.site_xpos[[2, 3], 2],
+                       rear_hip_y=d.xpos[[8, 11], 1], rear_hip_z=d.xpos[[8, 11], 2], front_hip_z=d.xpos[[2, 5], 2])
+        # time_unhealthy accumulates 0.02 s per step in the reference; k * 0.02 differs from the running sum only in the last bits,
+        # so the 750 -> 751 transition is decided on the step COUNT (tests/test_env_logic.py::test_termination_needs_751_unhealthy_steps)
+        o_obs, o_rew, o_term, o_trunc, o_info = logic.step(ep, act[e].astype(np.float64), d.qpos.copy(), d.qvel.copy(), d.qacc.copy(),
+                                                           d.qfrc_actuator.copy(), d.cfrc_ext.copy(), d.xpos[1, 2], kin=kin)
+        o_term = (p["unhealthy"] + 1 > 750) if not o_info["healthy"] else False
+        feet = np.linalg.norm(d.cfrc_ext[[4, 7, 10, 13]], axis=1)
+        if np.any(np.abs(feet - 1.0) < 1e-3) or abs(np.linalg.norm(d.cfrc_ext[[2, 3, 5, 6, 8, 9, 11, 12]]) - 0.1) < 1e-3:
+            continue      # a contact-force threshold within fp32 rounding: either side is legitimate
+        checked += 1
+        o_done = bool(o_term or o_trunc)
+        flags["done"] += int(bool(done[e]) != o_done)
+        flags["trunc"] += int(bool(trunc[e]) != bool(o_trunc and not o_term))
+        flags["healthy"] += int(bool(info[e, 13] > 0.5) != bool(o_info["healthy"]))
+        got_obs = tobs[e] if o_done else obs[e]
+        worst["obs"] = max(worst["obs"], float(np.abs(got_obs - o_obs).max()))
+        worst["reward"] = max(worst["reward"], abs(float(rew[e]) - o_rew) / max(1.0, abs(o_rew)))
+        keys = el.INFO_KEYS[:6] if biped else el.INFO_KEYS
+        gi = np.array([o_info[k] for k in keys])
+        worst["info"] = max(worst["info"], float((np.abs(info[e, 2:2 + len(keys)] - gi) / np.maximum(1.0, np.abs(gi))).max()))
+        if biped:
+            gb = np.array([o_info[k] for k in el.BIPED_INFO_KEYS])
+            worst["binfo"] = max(worst["binfo"], float((np.abs(binfo[e, :10] - gb) / np.maximum(1.0, np.abs(gb))).max()))
+            flags["success"] += int(bool(binfo[e, 10] > 0.5) != bool(o_info["bipedal_success"]))
+            if not o_done:
+                flags["fft"] += int(bool(binfo[e, 11] > 0.5) != bool(p["fft"] or np.any(feet[:2] > 1.0)))
+        if not o_done:
+            st = sim.get_state(e)
+            worst["air"] = max(worst["air"], float(np.abs(st["feet_air_time"] - ep.feet_air_time).max()))
+            worst["dev"] = max(worst["dev"], float(np.abs(st["last_health_deviation"] - ep.last_dev).max()))
+            flags["last_contacts"] += int(np.any(st["last_contacts"].astype(bool) != ep.last_contacts))
+            flags["unhealthy"] += int(st["unhealthy_steps"] != (0 if o_info["healthy"] else p["unhealthy"] + 1))
+    sim.close()
+    assert checked >= n * 0.8, checked
+    assert all(v == 0 for v in flags.values()), flags
+    for k, t in tol.items():
+        assert worst[k] <= t, (ctrl, biped, k, worst[k])
+    return worst
+
+
+EL64 = dict(obs=2e-6, reward=2e-6, info=2e-6, binfo=2e-6, air=1e-12, dev=1e-12)       # f32 output buffers
+# ten fp32 mj_steps from violent random states.  binfo: unwanted_contact = 150 |cfrc_ext|^2 carries twice the relative error of
+# cfrc_ext, whose WORST case over such states is 2e-2 (a 1e3 N impact wrench resolved by an fp32 solve; median 3e-4)
+EL32 = dict(obs=2e-5, reward=5e-4, info=2e-5, binfo=5e-2, air=1e-6, dev=1e-6)      # measured on the GPU: 4e-6, 7e-5, 2e-6, 8e-3, 5e-8, 3e-7
+
+
+@pytest.mark.parametrize("biped", [False, True])
+def test_env_logic_random_states_emu_f64(emu_lib_f64, biped):
+    _run_env_logic(emu_lib_f64, "torque", biped, 48, seed=21, tol=EL64)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("biped", [False, True])
+@pytest.mark.parametrize("ctrl", ["torque", "position"])
+def test_env_logic_random_states_gpu(cuda_lib_f64, cuda_lib_f32, ctrl, biped):
+    w64 = _run_env_logic(cuda_lib_f64, ctrl, biped, 512, seed=22, tol=EL64)
+    w32 = _run_env_logic(cuda_lib_f32, ctrl, biped, 512, seed=23, tol=EL32)
+    print(ctrl, "biped" if biped else "quadruped", "f64", {k: float("%.2g" % v) for k, v in w64.items()}, "f32", {k: float("%.2g" % v) for k, v in w32.items()})

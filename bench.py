@@ -29,6 +29,10 @@ UNIT = "env-steps/s"
 ENVS_PER_GPU = 16384
 ALG_BYTES_PER_ENV_STEP = 904.0     # 82 state words r+w, 12 action floats in, obs/reward/flags out
 ALG_FLOP_PER_ENV_STEP = 0.67e6     # SURVEY 8(d) nominal (10 substeps x (25k + 3 Newton iterations x 14k))
+# FP32 operations the kernel actually EXECUTES per env-step (fadd + fmul + 2 ffma, predicated-on threads) in the committed
+# ncu capture (profiles/r1_ncu_k_step_final_raw_selected.txt): 1.885e10 per launch of 16384 envs; 3.7 iterations per substep
+# instead of the nominal 3 and the redundancy of lane-parallel evaluation make up the difference to the nominal figure
+NCU_EXECUTED_FLOP_PER_ENV_STEP = 1.15e6
 # dram__bytes_read.sum + dram__bytes_write.sum of ONE k_step launch at 16384 envs, from the committed ncu --set full capture
 # (profiles/r1_ncu_k_step_final_raw_selected.txt): 9.96 MB + 18.08 MB
 NCU_DRAM_BYTES_PER_LAUNCH_16K = 28.05e6
@@ -254,7 +258,9 @@ def run_ours(args, rank, world, local):
                          "note": "neither HBM nor FP32 binds: the GPC instruction cache does (gcc instruction requests at 80 % of "
                                  "peak, DESIGN.md section 3); see fp32 block",
                          "fp32": {"achieved_tflops": ach_tf, "peak_tflops": fp32_peak, "frac": ach_tf / fp32_peak,
-                                  "flop_per_env_step": ALG_FLOP_PER_ENV_STEP, "peak": "n_SM*128*2*f_max (nominal)", "sm_mhz_under_load": sm_mhz}},
+                                  "flop_per_env_step": ALG_FLOP_PER_ENV_STEP, "executed_flop_per_env_step_ncu": NCU_EXECUTED_FLOP_PER_ENV_STEP,
+                                  "executed_tflops": NCU_EXECUTED_FLOP_PER_ENV_STEP * n / (per_launch_ms * 1e-3) / 1e12,
+                                  "peak": "n_SM*128*2*f_max (nominal)", "sm_mhz_under_load": sm_mhz}},
             "cpu_baseline": {"value": cpu_v, "unit": UNIT, "cores": cores, "kind": "port",
                              "sample": f"fp64 oracle (restatement, not MuJoCo): {cores} envs on {cores} threads, {cpu_n} control steps in {cpu_dt:.1f} s, physics only"},
             "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": n * 12 * 4,

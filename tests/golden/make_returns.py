@@ -2,7 +2,7 @@
 position-control policies (``models/**/final_model.zip``) in the reference's own environment code
 (unmodified ``go1_mujoco_env.py``, imported from /root/reference) on the fp64 oracle physics.
 
-    python tests/golden/make_returns.py [n_episodes=1000] [n_procs=8] [max_steps=1500]
+    python tests/golden/make_returns.py [n_episodes=1000] [n_procs=8] [max_steps=1500] [tag,tag,... = all]
 
 north_star's third correctness criterion: the CUDA simulator must reproduce the MEAN episode return of these
 policies within 2 % (trajectories are chaotic, so only the statistics are comparable).  Episodes are capped at
@@ -31,6 +31,8 @@ OUT = os.path.join(ROOT, "tests", "golden")
 POLICIES = {
     "pos_0428": "models/2024-04-28_22-10-59=1_pos_ctrl_20mil_iter_walking_with_normal_steps/final_model.zip",
     "pos_0421": "models/2024-04-21_20-04-20=1_pso_ctrl_30mil_iter_walking_with_oriented_rear_legs/final_model.zip",
+    "pos_0427": "models/2024-04-27_18-04-12=1_pos_ctrl_20mil_iter_walking_with_fast_steps/final_model.zip",
+    "pos_0428_best": "models/2024-04-28_22-10-59=1_pos_ctrl_20mil_iter_walking_with_normal_steps/best_model.zip",
 }
 V_DES = (0.5, 0.0, 0.0)
 RAND_POWER = 1.0     # reset joint noise N(0, 0.1 rad) (go1_mujoco_env.py:974-982): without it every upright episode of a
@@ -81,11 +83,14 @@ def main():
     n_ep = int(sys.argv[1]) if len(sys.argv) > 1 else 1000
     procs = int(sys.argv[2]) if len(sys.argv) > 2 else 8
     max_steps = int(sys.argv[3]) if len(sys.argv) > 3 else 1500
+    only = sys.argv[4].split(",") if len(sys.argv) > 4 else list(POLICIES)
     for tag, rel in POLICIES.items():
+        if tag not in only:
+            continue
         pol = load_policy(os.path.join("/root/reference", rel))
         assert pol["w0"].shape == (64, 48) and pol["w2"].shape == (12, 64)
         np.savez(os.path.join(OUT, f"policy_{tag}.npz"), **pol)
-    for tag in POLICIES:
+    for tag in only:
         seeds = np.arange(n_ep) + 1000
         chunks = [(tag, list(map(int, c)), max_steps) for c in np.array_split(seeds, procs * 4)]
         with mp.Pool(procs) as pool:

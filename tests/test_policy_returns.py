@@ -18,7 +18,7 @@ import pytest
 import parity_common as pc
 from quadruped_rl_locomotion_b200.vec_env import Go1CudaVecEnv
 
-TAGS = ("pos_0428", "pos_0421")
+TAGS = ("pos_0428", "pos_0421", "pos_0427", "pos_0428_best")     # the three 48-d position final_model.zip + the 04-28 best_model.zip
 
 
 def _policy(tag):

@@ -33,6 +33,7 @@ ALG_FLOP_PER_ENV_STEP = 0.67e6     # SURVEY 8(d) nominal (10 substeps x (25k + 3
 # ncu capture (profiles/r1_ncu_k_step_final_raw_selected.txt): 1.885e10 per launch of 16384 envs; 3.7 iterations per substep
 # instead of the nominal 3 and the redundancy of lane-parallel evaluation make up the difference to the nominal figure
 NCU_EXECUTED_FLOP_PER_ENV_STEP = 1.15e6
+FP32_FMA_MEASURED_TFLOPS = 72.1    # tools/ubench/fma.cu on this pool's B200 (148 SMs, 1965 MHz): 97 % of 148 x 128 x 2 x 1.965 GHz
 # dram__bytes_read.sum + dram__bytes_write.sum of ONE k_step launch at 16384 envs, from the committed ncu --set full capture
 # (profiles/r1_ncu_k_step_final_raw_selected.txt): 9.96 MB + 18.08 MB
 NCU_DRAM_BYTES_PER_LAUNCH_16K = 28.05e6
@@ -241,7 +242,8 @@ def run_ours(args, rank, world, local):
         ach_gbs = ALG_BYTES_PER_ENV_STEP * n / (per_launch_ms * 1e-3) / 1e9
         sm_mhz = clk.get("sm_mhz") or peaks.get("sm_max_mhz", 1965.0)
         nsm = torch.cuda.get_device_properties(local).multi_processor_count
-        fp32_peak = nsm * 128 * 2 * peaks.get("sm_max_mhz", 1965.0) * 1e6 / 1e12
+        fp32_nominal = nsm * 128 * 2 * peaks.get("sm_max_mhz", 1965.0) * 1e6 / 1e12
+        fp32_peak = FP32_FMA_MEASURED_TFLOPS if nsm == 148 else fp32_nominal
         ach_tf = ALG_FLOP_PER_ENV_STEP * n / (per_launch_ms * 1e-3) / 1e12
         cores = os.cpu_count() or 1
         cpu_v, cpu_n, cpu_dt = cpu_port_rate(float(os.environ.get("GO1_CPU_BASELINE_SECONDS", "12")), cores, args.ctrl)
@@ -260,7 +262,8 @@ def run_ours(args, rank, world, local):
                          "fp32": {"achieved_tflops": ach_tf, "peak_tflops": fp32_peak, "frac": ach_tf / fp32_peak,
                                   "flop_per_env_step": ALG_FLOP_PER_ENV_STEP, "executed_flop_per_env_step_ncu": NCU_EXECUTED_FLOP_PER_ENV_STEP,
                                   "executed_tflops": NCU_EXECUTED_FLOP_PER_ENV_STEP * n / (per_launch_ms * 1e-3) / 1e12,
-                                  "peak": "n_SM*128*2*f_max (nominal)", "sm_mhz_under_load": sm_mhz}},
+                                  "peak": "measured FMA throughput (tools/ubench/fma.cu, profiles/r1_fma_ubench.json)" if nsm == 148 else "n_SM*128*2*f_max (nominal)",
+                                  "nominal_peak_tflops": fp32_nominal, "sm_mhz_under_load": sm_mhz}},
             "cpu_baseline": {"value": cpu_v, "unit": UNIT, "cores": cores, "kind": "port",
                              "sample": f"fp64 oracle (restatement, not MuJoCo): {cores} envs on {cores} threads, {cpu_n} control steps in {cpu_dt:.1f} s, physics only"},
             "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": n * 12 * 4,

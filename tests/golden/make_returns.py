@@ -33,6 +33,10 @@ POLICIES = {
     "pos_0421": "models/2024-04-21_20-04-20=1_pso_ctrl_30mil_iter_walking_with_oriented_rear_legs/final_model.zip",
     "pos_0427": "models/2024-04-27_18-04-12=1_pos_ctrl_20mil_iter_walking_with_fast_steps/final_model.zip",
     "pos_0428_best": "models/2024-04-28_22-10-59=1_pos_ctrl_20mil_iter_walking_with_normal_steps/best_model.zip",
+    # not a reference artefact: trained HERE by examples/train_ppo.py on the CUDA environments (200 M steps, 16384 envs, one B200,
+    # position control, rand_power 1); policy_ppo_b200.npz is committed.  Evaluated in the reference env like the shipped ones
+    # ("eval of the trained policy in both simulators").
+    "ppo_b200": None,
 }
 V_DES = (0.5, 0.0, 0.0)
 RAND_POWER = 1.0     # reset joint noise N(0, 0.1 rad) (go1_mujoco_env.py:974-982): without it every upright episode of a
@@ -85,7 +89,7 @@ def main():
     max_steps = int(sys.argv[3]) if len(sys.argv) > 3 else 1500
     only = sys.argv[4].split(",") if len(sys.argv) > 4 else list(POLICIES)
     for tag, rel in POLICIES.items():
-        if tag not in only:
+        if tag not in only or rel is None:
             continue
         pol = load_policy(os.path.join("/root/reference", rel))
         assert pol["w0"].shape == (64, 48) and pol["w2"].shape == (12, 64)

@@ -18,7 +18,9 @@ import pytest
 import parity_common as pc
 from quadruped_rl_locomotion_b200.vec_env import Go1CudaVecEnv
 
-TAGS = ("pos_0428", "pos_0421", "pos_0427", "pos_0428_best")     # the three 48-d position final_model.zip + the 04-28 best_model.zip
+# + "ppo_b200": a policy trained HERE on the CUDA environments (examples/train_ppo.py, 200 M steps) and evaluated in the
+# reference env code afterwards: the transfer direction SURVEY 8(d) config 5 asks for
+TAGS = ("pos_0428", "pos_0421", "pos_0427", "pos_0428_best", "ppo_b200")     # the three 48-d position final_model.zip + the 04-28 best_model.zip
 
 
 def _policy(tag):

@@ -12,13 +12,14 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 SRC = os.path.join(HERE, "csrc", "go1sim.cu")
 DEPS = [SRC, os.path.join(HERE, "csrc", "go1_warp.cuh"), os.path.join(HERE, "csrc", "go1_model.h"),
-        os.path.join(os.path.dirname(HERE), "include", "go1sim.h")]
+        os.path.join(os.path.dirname(HERE), "include", "go1sim.h"), os.path.abspath(__file__)]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-Xcompiler", "-fPIC",
               "-shared", "--expt-relaxed-constexpr"]
 
 
-# fp32 product build: MUFU-based division / square root (<= 2 ulp) instead of the IEEE slow paths
-F32_FLAGS = ["-prec-div=false", "-prec-sqrt=false"]
+# fp32 product build: MUFU-based division / square root (<= 2 ulp) instead of the IEEE slow paths, denormals flushed to zero
+# (drops the denormal fix-up code of those sequences: -2 % kernel time, parity unchanged; quantities here are never < 1e-38)
+F32_FLAGS = ["-prec-div=false", "-prec-sqrt=false", "-ftz=true"]
 
 
 def _stale(out: str) -> bool:

@@ -19,8 +19,9 @@
  * model constants (tests/test_mjcf.py), (ii) physics invariants (tests/test_oracle.py: mass
  * matrix vs independent Jacobian formula, momentum/energy, KKT residual, cone membership).
  *
- * Deliberate scope limit (documented in DESIGN.md): robot self-collision pairs are not
- * generated; only plane-vs-geom pairs are (north_star: "plane-vs-geom narrowphase").
+ * Robot-robot pairs (every collision geom has contype = conaffinity = 1, go1_torque.xml:9,26) are
+ * generated for all bodies that are not parent and child; pairs with a cylinder use the exact
+ * closest-feature solution in place of MuJoCo 2.3.0's MPR (see the narrowphase section).
  *
  * Build: see oracle/Makefile (gcc -O2 -shared -fPIC).
  */
@@ -84,7 +85,7 @@ typedef struct {
     double *efc_J, *efc_pos, *efc_margin, *efc_frictionloss, *efc_diagApprox, *efc_R, *efc_D, *efc_KBIP;
     double *efc_vel, *efc_aref, *efc_force;
     int *efc_type, *efc_id, *efc_state;
-    int solver_iter, ls_total, warn_bad, warn_contact_full;
+    int solver_iter, ls_total, warn_bad, warn_contact_full, warn_unsupported_pair, self_collision;
     double solver_improvement, solver_gradient;
     /* optional overrides used by tests */
     double tolerance_override; /* <0: use model */
@@ -197,6 +198,7 @@ EXPORT O1Data *o1_data_new(const O1Model *m) {
     d->efc_type = (int *)calloc(MAXEFC, sizeof(int)); d->efc_id = (int *)calloc(MAXEFC, sizeof(int));
     d->efc_state = (int *)calloc(MAXEFC, sizeof(int));
     d->tolerance_override = -1.0;
+    d->self_collision = 1;
     return d;
 }
 
@@ -628,6 +630,180 @@ static void makeFrame(double *f) {
     cross3(f + 6, f, f + 3);
 }
 
+/* ------------------------------------------------------------------------------------------ */
+/* robot-robot narrowphase (engine_collision_primitive.c / engine_collision_box.c).  The normal points
+ * from geom1 to geom2 (type1 <= type2 after mj_collideGeoms' swap).  sphere-sphere, sphere-capsule,
+ * capsule-capsule and sphere-box restate MuJoCo's analytic functions [recalled].  MuJoCo 2.3.0 sends every
+ * pair with a cylinder other than plane-cylinder through libccd's MPR (mjc_Convex, one contact, tolerance
+ * 1e-6), which cannot be reproduced analytically: here those pairs use the exact closest-feature solution
+ * that MPR approximates (point / segment vs solid cylinder, one contact).  capsule-box: closest point of
+ * the segment to the box, then sphere-box there, plus the far end of the capsule when it is within the
+ * margin as well (MuJoCo's mjc_CapsuleBox also returns up to two contacts, its second-contact rule is
+ * restated in simplified form).  The CUDA kernel implements exactly the same rules (go1_pair.cuh). */
+static int sphereSphereRaw(const double *c1, double r1, const double *c2, double r2, const double *fall1, const double *fall2,
+                           double margin, RawCon *con) {
+    double dif[3] = {c2[0] - c1[0], c2[1] - c1[1], c2[2] - c1[2]};
+    double cd2 = dot3(dif, dif), md = margin + r1 + r2;
+    if (cd2 > md * md) return 0;
+    double len = sqrt(cd2);
+    con->dist = len - r1 - r2;
+    memset(con->frame, 0, sizeof con->frame);
+    if (len < mjMINVAL) {   /* coincident centres: cross product of the z axes (mjraw_SphereSphere) */
+        cross3(con->frame, fall1, fall2);
+        normalize3(con->frame);
+    } else for (int k = 0; k < 3; k++) con->frame[k] = dif[k] / len;
+    for (int k = 0; k < 3; k++) con->pos[k] = c1[k] + con->frame[k] * (r1 + 0.5 * con->dist);
+    return 1;
+}
+static int mjc_SphereCapsule(const double *p1, const double *m1, double r1, const double *p2, const double *m2, const double *s2,
+                             double margin, RawCon *con) {
+    double ax[3] = {m2[2], m2[5], m2[8]}, v[3] = {p1[0] - p2[0], p1[1] - p2[1], p1[2] - p2[2]};
+    double x = fmin(s2[1], fmax(-s2[1], dot3(ax, v)));
+    double q[3] = {p2[0] + ax[0] * x, p2[1] + ax[1] * x, p2[2] + ax[2] * x};
+    double z1[3] = {m1[2], m1[5], m1[8]};
+    return sphereSphereRaw(p1, r1, q, s2[0], z1, ax, margin, con);
+}
+static int mjc_CapsuleCapsule(const double *p1, const double *m1, const double *s1, const double *p2, const double *m2, const double *s2,
+                              double margin, RawCon *con) {
+    double z1[3] = {m1[2], m1[5], m1[8]}, z2[3] = {m2[2], m2[5], m2[8]};
+    double a1[3] = {z1[0] * s1[1], z1[1] * s1[1], z1[2] * s1[1]}, a2[3] = {z2[0] * s2[1], z2[1] * s2[1], z2[2] * s2[1]};
+    double dif[3] = {p1[0] - p2[0], p1[1] - p2[1], p1[2] - p2[2]};
+    double ma = dot3(a1, a1), mb = -dot3(a1, a2), mc = dot3(a2, a2), u = -dot3(a1, dif), v = dot3(a2, dif);
+    double det = ma * mc - mb * mb;
+    double v1[3], v2[3];
+    if (fabs(det) >= mjMINVAL) {
+        double x1 = (mc * u - mb * v) / det, x2 = (ma * v - mb * u) / det;
+        if (x1 > 1) { x1 = 1; x2 = (v - mb) / mc; }
+        else if (x1 < -1) { x1 = -1; x2 = (v + mb) / mc; }
+        if (x2 > 1) { x2 = 1; x1 = (u - mb) / ma; }
+        else if (x2 < -1) { x2 = -1; x1 = (u + mb) / ma; }
+        x1 = fmin(1.0, fmax(-1.0, x1));
+        for (int k = 0; k < 3; k++) { v1[k] = p1[k] + a1[k] * x1; v2[k] = p2[k] + a2[k] * x2; }
+        return sphereSphereRaw(v1, s1[0], v2, s2[0], z1, z2, margin, con);
+    }
+    /* parallel axes: up to two contacts from the four end-point projections */
+    int n = 0;
+    for (int e = 0; e < 4 && n < 2; e++) {
+        double x1, x2;
+        if (e == 0) { x1 = 1; x2 = (v - mb) / mc; x2 = fmin(1.0, fmax(-1.0, x2)); }
+        else if (e == 1) { x1 = -1; x2 = (v + mb) / mc; x2 = fmin(1.0, fmax(-1.0, x2)); }
+        else if (e == 2) { x2 = 1; x1 = (u - mb) / ma; x1 = fmin(1.0, fmax(-1.0, x1)); }
+        else { x2 = -1; x1 = (u + mb) / ma; x1 = fmin(1.0, fmax(-1.0, x1)); }
+        for (int k = 0; k < 3; k++) { v1[k] = p1[k] + a1[k] * x1; v2[k] = p2[k] + a2[k] * x2; }
+        n += sphereSphereRaw(v1, s1[0], v2, s2[0], z1, z2, margin, con + n);
+    }
+    return n;
+}
+/* sphere (centre c, radius r) vs box (p2, m2, half sizes s2): mjc_SphereBox */
+static int sphereBoxRaw(const double *c, double r, const double *p2, const double *m2, const double *s2, double margin, RawCon *con) {
+    double t[3] = {c[0] - p2[0], c[1] - p2[1], c[2] - p2[2]}, ctr[3], cl[3], dv[3];
+    for (int i = 0; i < 3; i++) ctr[i] = m2[i] * t[0] + m2[3 + i] * t[1] + m2[6 + i] * t[2];   /* box frame */
+    for (int i = 0; i < 3; i++) { cl[i] = fmin(s2[i], fmax(-s2[i], ctr[i])); dv[i] = cl[i] - ctr[i]; }
+    double dist = norm3(dv), nl[3];
+    if (dist - r > margin) return 0;
+    memset(con->frame, 0, sizeof con->frame);
+    double pl[3];
+    if (dist <= mjMINVAL) {   /* centre inside the box: leave through the nearest face */
+        double closest = 1e30; int k = 0;
+        for (int i = 0; i < 6; i++) {
+            double fd = fabs((i % 2 ? 1.0 : -1.0) * s2[i / 2] - ctr[i / 2]);
+            if (fd < closest) { closest = fd; k = i; }
+        }
+        nl[0] = nl[1] = nl[2] = 0; nl[k / 2] = (k % 2) ? -1.0 : 1.0;
+        con->dist = -closest - r;
+        for (int i = 0; i < 3; i++) pl[i] = ctr[i] + nl[i] * (r - closest) * 0.5;
+    } else {
+        for (int i = 0; i < 3; i++) nl[i] = dv[i] / dist;
+        con->dist = dist - r;
+        for (int i = 0; i < 3; i++) pl[i] = ctr[i] + nl[i] * (r + 0.5 * con->dist);
+    }
+    mulMatVec3(con->frame, m2, nl);
+    double pw[3]; mulMatVec3(pw, m2, pl);
+    for (int k = 0; k < 3; k++) con->pos[k] = pw[k] + p2[k];
+    return 1;
+}
+/* sphere vs solid cylinder (p2, axis = z column of m2, radius s2[0], half length s2[1]) */
+static int sphereCylinderRaw(const double *c, double r, const double *p2, const double *m2, const double *s2, double margin, RawCon *con) {
+    double ax[3] = {m2[2], m2[5], m2[8]}, t[3] = {c[0] - p2[0], c[1] - p2[1], c[2] - p2[2]};
+    double z = dot3(ax, t), w[3] = {t[0] - z * ax[0], t[1] - z * ax[1], t[2] - z * ax[2]};
+    double rho = norm3(w), R = s2[0], h = s2[1], e[3];
+    if (rho < mjMINVAL) { e[0] = m2[0]; e[1] = m2[3]; e[2] = m2[6]; } else { e[0] = w[0] / rho; e[1] = w[1] / rho; e[2] = w[2] / rho; }
+    double dz = fabs(z) - h, dr = rho - R, sz = z < 0 ? -1.0 : 1.0, n[3];
+    memset(con->frame, 0, sizeof con->frame);
+    if (dz <= 0 && dr <= 0) {     /* centre inside: leave through the nearer of side and cap */
+        double closest;
+        if (-dr < -dz) { closest = -dr; for (int k = 0; k < 3; k++) n[k] = -e[k]; }
+        else { closest = -dz; for (int k = 0; k < 3; k++) n[k] = -sz * ax[k]; }
+        if (-closest - r > margin) return 0;
+        con->dist = -closest - r;
+        for (int k = 0; k < 3; k++) con->pos[k] = c[k] + n[k] * (r - closest) * 0.5;
+    } else {
+        double zc = fmin(h, fmax(-h, z)), rc = fmin(rho, R), q[3], dv[3];
+        for (int k = 0; k < 3; k++) { q[k] = p2[k] + zc * ax[k] + rc * e[k]; dv[k] = q[k] - c[k]; }
+        double dist = norm3(dv);
+        if (dist - r > margin) return 0;
+        if (dist < mjMINVAL) return 0;
+        for (int k = 0; k < 3; k++) n[k] = dv[k] / dist;
+        con->dist = dist - r;
+        for (int k = 0; k < 3; k++) con->pos[k] = c[k] + n[k] * (r + 0.5 * con->dist);
+    }
+    memcpy(con->frame, n, 24);
+    return 1;
+}
+/* d/dt of half the squared distance between the capsule-axis point pc + t*av (t in [-1, 1]) and a box /
+ * cylinder given in ITS frame (pl = pc, al = av in that frame; cylinder: box == 0, sz = {R, R, h}) */
+static double seg_grad(const double *pl, const double *al, const double *sz, int box, double t) {
+    double x[3] = {pl[0] + t * al[0], pl[1] + t * al[1], pl[2] + t * al[2]};
+    if (box) {
+        double g = 0;
+        for (int i = 0; i < 3; i++) { double ex = x[i] - fmin(sz[i], fmax(-sz[i], x[i])); g += ex * al[i]; }
+        return g;
+    }
+    double rho = sqrt(x[0] * x[0] + x[1] * x[1]);
+    double ez = x[2] - fmin(sz[2], fmax(-sz[2], x[2])), g = ez * al[2];
+    if (rho > sz[0]) g += (rho - sz[0]) * (x[0] * al[0] + x[1] * al[1]) / rho;
+    return g;
+}
+#define SEG_BISECT 40
+/* parameter of the capsule-axis point closest to the box / cylinder (convex 1-D problem: bisection on the sign of the
+ * derivative, fixed trip count so that the kernel and the oracle take the same path) */
+static double seg_closest(const double *pl, const double *al, const double *sz, int box) {
+    double glo = seg_grad(pl, al, sz, box, -1.0), ghi = seg_grad(pl, al, sz, box, 1.0);
+    if (glo >= 0) return -1.0;
+    if (ghi <= 0) return 1.0;
+    double lo = -1.0, hi = 1.0;
+    for (int it = 0; it < SEG_BISECT; it++) {
+        double mid = 0.5 * (lo + hi);
+        if (seg_grad(pl, al, sz, box, mid) < 0) lo = mid; else hi = mid;
+    }
+    return 0.5 * (lo + hi);
+}
+/* capsule (geom1) vs box or cylinder (geom2) */
+static int capsuleConvex(const double *p1, const double *m1, const double *s1, const double *p2, const double *m2, const double *s2,
+                         int box, double margin, RawCon *con) {
+    double ax[3] = {m1[2], m1[5], m1[8]}, t[3] = {p1[0] - p2[0], p1[1] - p2[1], p1[2] - p2[2]}, pl[3], al[3];
+    for (int i = 0; i < 3; i++) {
+        pl[i] = m2[i] * t[0] + m2[3 + i] * t[1] + m2[6 + i] * t[2];
+        al[i] = (m2[i] * ax[0] + m2[3 + i] * ax[1] + m2[6 + i] * ax[2]) * s1[1];
+    }
+    double sz[3] = {s2[0], box ? s2[1] : s2[0], box ? s2[2] : s2[1]};
+    /* separating-axis prefilter on the face normals of the (bounding) box */
+    for (int i = 0; i < 3; i++) {
+        double lim = sz[i] + s1[0] + margin, a = pl[i] - al[i], b = pl[i] + al[i];
+        if ((a > lim && b > lim) || (a < -lim && b < -lim)) return 0;
+    }
+    double ts = seg_closest(pl, al, sz, box);
+    int n = 0;
+    for (int e = 0; e < 2; e++) {
+        double tt = e == 0 ? ts : (ts >= 0 ? -1.0 : 1.0);
+        if (e == 1 && !box) break;            /* cylinder pairs: one contact (as MPR) */
+        double c[3] = {p1[0] + ax[0] * s1[1] * tt, p1[1] + ax[1] * s1[1] * tt, p1[2] + ax[2] * s1[1] * tt};
+        n += box ? sphereBoxRaw(c, s1[0], p2, m2, s2, margin, con + n) : sphereCylinderRaw(c, s1[0], p2, m2, s2, margin, con + n);
+        if (e == 0 && n == 0) break;
+    }
+    return n;
+}
+
 /* contact parameter mixing (mj_contactParam semantics) + add contacts for one geom pair */
 static void collide_pair(O1Data *d, int g1, int g2) {
     const O1Model *m = d->m;
@@ -635,22 +811,56 @@ static void collide_pair(O1Data *d, int g1, int g2) {
     if (!((m->geom_contype[g1] & m->geom_conaffinity[g2]) || (m->geom_contype[g2] & m->geom_conaffinity[g1]))) return;
     double margin = fmax(m->geom_margin[g1], m->geom_margin[g2]);
     double gap = fmax(m->geom_gap[g1], m->geom_gap[g2]);
-    /* bounding-sphere vs plane filter */
-    {
-        const double *pp = d->geom_xpos + 3 * g1, *pm = d->geom_xmat + 9 * g1, *c = d->geom_xpos + 3 * g2;
-        double n[3] = {pm[2], pm[5], pm[8]}, t[3] = {c[0] - pp[0], c[1] - pp[1], c[2] - pp[2]};
-        if (dot3(t, n) > margin + m->geom_rbound[g2]) return;
-    }
+    /* mj_collideGeoms: the lower geom type is geom1 */
+    if (m->geom_type[g1] > m->geom_type[g2]) { int t_ = g1; g1 = g2; g2 = t_; }
     RawCon raw[8];
     int num = 0;
-    const double *p1 = d->geom_xpos + 3 * g1, *m1 = d->geom_xmat + 9 * g1;
+    const double *p1 = d->geom_xpos + 3 * g1, *m1 = d->geom_xmat + 9 * g1, *s1 = m->geom_size + 3 * g1;
     const double *p2 = d->geom_xpos + 3 * g2, *m2 = d->geom_xmat + 9 * g2, *s2 = m->geom_size + 3 * g2;
-    switch (m->geom_type[g2]) {
-        case GEOM_SPHERE: num = mjc_PlaneSphere(p1, m1, p2, s2, margin, raw); break;
-        case GEOM_CAPSULE: num = mjc_PlaneCapsule(p1, m1, p2, m2, s2, margin, raw); break;
-        case GEOM_CYLINDER: num = mjc_PlaneCylinder(p1, m1, p2, m2, s2, margin, raw); break;
-        case GEOM_BOX: num = mjc_PlaneBox(p1, m1, p2, m2, s2, margin, raw); break;
-        default: return;
+    if (m->geom_type[g1] == GEOM_PLANE) {
+        /* bounding-sphere vs plane filter */
+        double n[3] = {m1[2], m1[5], m1[8]}, t[3] = {p2[0] - p1[0], p2[1] - p1[1], p2[2] - p1[2]};
+        if (dot3(t, n) > margin + m->geom_rbound[g2]) return;
+        switch (m->geom_type[g2]) {
+            case GEOM_SPHERE: num = mjc_PlaneSphere(p1, m1, p2, s2, margin, raw); break;
+            case GEOM_CAPSULE: num = mjc_PlaneCapsule(p1, m1, p2, m2, s2, margin, raw); break;
+            case GEOM_CYLINDER: num = mjc_PlaneCylinder(p1, m1, p2, m2, s2, margin, raw); break;
+            case GEOM_BOX: num = mjc_PlaneBox(p1, m1, p2, m2, s2, margin, raw); break;
+            default: return;
+        }
+    } else {
+        /* bounding-sphere filter */
+        double t[3] = {p2[0] - p1[0], p2[1] - p1[1], p2[2] - p1[2]}, bound = m->geom_rbound[g1] + m->geom_rbound[g2] + margin;
+        if (dot3(t, t) > bound * bound) return;
+        int t1 = m->geom_type[g1], t2 = m->geom_type[g2];
+        double z1[3] = {m1[2], m1[5], m1[8]}, z2[3] = {m2[2], m2[5], m2[8]};
+        if (t1 == GEOM_SPHERE && t2 == GEOM_SPHERE) num = sphereSphereRaw(p1, s1[0], p2, s2[0], z1, z2, margin, raw);
+        else if (t1 == GEOM_SPHERE && t2 == GEOM_CAPSULE) num = mjc_SphereCapsule(p1, m1, s1[0], p2, m2, s2, margin, raw);
+        else if (t1 == GEOM_SPHERE && t2 == GEOM_CYLINDER) num = sphereCylinderRaw(p1, s1[0], p2, m2, s2, margin, raw);
+        else if (t1 == GEOM_SPHERE && t2 == GEOM_BOX) num = sphereBoxRaw(p1, s1[0], p2, m2, s2, margin, raw);
+        else if (t1 == GEOM_CAPSULE && t2 == GEOM_CAPSULE) num = mjc_CapsuleCapsule(p1, m1, s1, p2, m2, s2, margin, raw);
+        else if (t1 == GEOM_CAPSULE && t2 == GEOM_CYLINDER) num = capsuleConvex(p1, m1, s1, p2, m2, s2, 0, margin, raw);
+        else if (t1 == GEOM_CAPSULE && t2 == GEOM_BOX) num = capsuleConvex(p1, m1, s1, p2, m2, s2, 1, margin, raw);
+        else if (t1 == GEOM_CYLINDER && t2 == GEOM_CYLINDER) {
+            /* hip-vs-hip only (MuJoCo: MPR).  Separating-axis tests with the cylinders' support functions along the centre
+             * line, both axes and their cross product; a pair none of them separates (rear hip motors with both abduction
+             * joints within ~0.1 rad of their opposite limits) is COUNTED in warn_unsupported_pair, not collided */
+            double ax4[4][3];
+            double len = sqrt(dot3(t, t));
+            if (len < mjMINVAL) { d->warn_unsupported_pair++; return; }
+            for (int k = 0; k < 3; k++) { ax4[0][k] = t[k] / len; ax4[1][k] = z1[k]; ax4[2][k] = z2[k]; }
+            cross3(ax4[3], z1, z2);
+            if (normalize3(ax4[3]) < 1e-9) memcpy(ax4[3], ax4[0], 24);
+            for (int a = 0; a < 4; a++) {
+                const double *u = ax4[a];
+                double c1 = dot3(z1, u), c2 = dot3(z2, u);
+                double reach = s1[1] * fabs(c1) + s1[0] * sqrt(fmax(0.0, 1 - c1 * c1)) + s2[1] * fabs(c2) + s2[0] * sqrt(fmax(0.0, 1 - c2 * c2));
+                if (fabs(dot3(t, u)) - reach > margin) return;
+            }
+            d->warn_unsupported_pair++;
+            return;
+        }
+        else { d->warn_unsupported_pair++; return; }   /* cylinder-box / box-box: no such non-adjacent pair on this robot */
     }
     if (!num) return;
     /* mix parameters */
@@ -698,16 +908,26 @@ static void collide_pair(O1Data *d, int g1, int g2) {
     }
 }
 
-/* mj_collision restricted to plane-vs-robot pairs, in MuJoCo's (body pair, geom) order */
+/* mj_collision: body pairs in (body1, body2) order (mj_broadphase's sorted list), filterBodyPair (same body, parent and
+ * child unless the parent is the world), then every geom pair of the two bodies through collide_pair.  With
+ * self_collision == 0 only the world-vs-robot pairs are visited (round-1 behaviour, kept for A/B tests). */
 static void o1_collision(O1Data *d) {
     const O1Model *m = d->m;
     d->ncon = 0;
-    for (int g1 = 0; g1 < m->ngeom; g1++) {
-        if (m->geom_type[g1] != GEOM_PLANE || m->geom_bodyid[g1] != 0) continue;
-        for (int g2 = 0; g2 < m->ngeom; g2++) {
-            if (m->geom_bodyid[g2] == 0) continue;
-            if (m->geom_type[g2] == GEOM_PLANE || m->geom_type[g2] == GEOM_MESH) continue;
-            collide_pair(d, g1, g2);
+    for (int b1 = 0; b1 < m->nbody; b1++) {
+        for (int b2 = b1 + 1; b2 < m->nbody; b2++) {
+            if (b1 != 0 && !d->self_collision) continue;
+            if (b1 != 0 && (m->body_parentid[b2] == b1 || m->body_parentid[b1] == b2)) continue;
+            for (int i1 = 0; i1 < m->body_geomnum[b1]; i1++) {
+                int g1 = m->body_geomadr[b1] + i1;
+                if (m->geom_type[g1] == GEOM_MESH) continue;
+                if (b1 == 0 && m->geom_type[g1] != GEOM_PLANE) continue;
+                for (int i2 = 0; i2 < m->body_geomnum[b2]; i2++) {
+                    int g2 = m->body_geomadr[b2] + i2;
+                    if (m->geom_type[g2] == GEOM_PLANE || m->geom_type[g2] == GEOM_MESH) continue;
+                    collide_pair(d, g1, g2);
+                }
+            }
         }
     }
 }
@@ -1443,7 +1663,7 @@ EXPORT double *o1_field(O1Data *d, const char *name, int *n) {
 EXPORT int *o1_ifield(O1Data *d, const char *name, int *n) {
 #define F(nm, cnt) if (strcmp(name, #nm) == 0) { if (n) *n = (cnt); return &d->nm; }
 #define FP(nm, cnt) if (strcmp(name, #nm) == 0) { if (n) *n = (cnt); return d->nm; }
-    F(ncon, 1) F(nefc, 1) F(nf, 1) F(solver_iter, 1) F(ls_total, 1) F(warn_bad, 1) F(warn_contact_full, 1)
+    F(ncon, 1) F(nefc, 1) F(nf, 1) F(solver_iter, 1) F(ls_total, 1) F(warn_bad, 1) F(warn_contact_full, 1) F(warn_unsupported_pair, 1) F(self_collision, 1)
     FP(efc_type, d->nefc) FP(efc_id, d->nefc) FP(efc_state, d->nefc)
 #undef F
 #undef FP

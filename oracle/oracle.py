@@ -97,7 +97,8 @@ class _Data:
 
     def __getattr__(self, name):
         sim = self._sim
-        if name in ("ncon", "nefc", "nf", "solver_iter", "ls_total", "warn_bad", "warn_contact_full"):
+        if name in ("ncon", "nefc", "nf", "solver_iter", "ls_total", "warn_bad", "warn_contact_full", "warn_unsupported_pair",
+                    "self_collision"):
             n = ctypes.c_int(0)
             return int(_lib().o1_ifield(sim._d, name.encode(), ctypes.byref(n))[0])
         if name in ("efc_type", "efc_id", "efc_state"):
@@ -159,6 +160,11 @@ class OracleSim:
 
     def rne_post_constraint(self):
         _lib().o1_rne_post_constraint(self._d)
+
+    def set_self_collision(self, on: bool):
+        """Robot-robot pairs on (default, MuJoCo's behaviour for this MJCF) or off (floor contacts only)."""
+        n = ctypes.c_int(0)
+        _lib().o1_ifield(self._d, b"self_collision", ctypes.byref(n))[0] = 1 if on else 0
 
     def set_tolerance(self, tol: float):
         """Test knob: override the Newton tolerance (negative -> model value)."""

@@ -50,8 +50,8 @@ def _snapshot_physics(env):
 def record_trace(env, actions, label):
     """Runs env.step over `actions`; returns dict of stacked arrays (index 0 = initial state)."""
     rec = {k: [v] for k, v in {**_snapshot_physics(env), **_snapshot_episode(env)}.items()}
-    post = {k: [] for k in ("action", "qacc", "qfrc_actuator", "cfrc_ext", "trunk_z", "ncon", "con_geom", "con_dist",
-                            "con_fn", "obs", "reward", "info", "healthy", "terminated", "truncated", "solver_iter")}
+    post = {k: [] for k in ("action", "qacc", "qfrc_actuator", "cfrc_ext", "trunk_z", "ncon", "con_geom", "con_geom1", "con_dim",
+                            "con_dist", "con_fn", "con_force", "con_pos", "obs", "reward", "info", "healthy", "terminated", "truncated", "solver_iter")}
     for a in actions:
         obs, reward, terminated, truncated, info = env.step(a)
         d = env.data
@@ -61,11 +61,14 @@ def record_trace(env, actions, label):
         post["qacc"].append(d.qacc.copy()); post["qfrc_actuator"].append(d.qfrc_actuator.copy())
         post["cfrc_ext"].append(d.cfrc_ext.copy()); post["trunk_z"].append(d.xpos[1, 2])
         cons = [c for c in d.contact if c.exclude == 0]
-        g = -np.ones(MAXC, np.int32); dist = np.zeros(MAXC); fn = np.zeros(MAXC)
+        g = -np.ones(MAXC, np.int32); g1 = -np.ones(MAXC, np.int32); dim = np.zeros(MAXC, np.int32)
+        dist = np.zeros(MAXC); fn = np.zeros(MAXC); frc = np.zeros((MAXC, 6)); cpos = np.zeros((MAXC, 3))
         f = d.efc_force
         for i, c in enumerate(cons[:MAXC]):
-            g[i] = c.geom2; dist[i] = c.dist; fn[i] = f[c.efc_address]
+            g[i] = c.geom2; g1[i] = c.geom1; dim[i] = c.dim; dist[i] = c.dist; fn[i] = f[c.efc_address]
+            frc[i, :c.dim] = f[c.efc_address:c.efc_address + c.dim]; cpos[i] = c.pos
         post["ncon"].append(len(cons)); post["con_geom"].append(g); post["con_dist"].append(dist); post["con_fn"].append(fn)
+        post["con_geom1"].append(g1); post["con_dim"].append(dim); post["con_force"].append(frc); post["con_pos"].append(cpos)
         post["obs"].append(obs.copy()); post["reward"].append(reward)
         post["info"].append(np.array([info.get(k, 0.0) for k in INFO_KEYS], dtype=np.float64))   # biped mode drops two keys
         post["healthy"].append(info["termination_reason"] == "not_terminated")
@@ -75,8 +78,9 @@ def record_trace(env, actions, label):
             break
     out = {k: np.array(v) for k, v in rec.items()}
     out.update({k: np.array(v) for k, v in post.items()})
+    nself = sum(int(np.sum(g1 > 0)) for g1 in post["con_geom1"])
     print(f"  {label}: {len(post['reward'])} steps, mean reward {np.mean(post['reward']):.4f}, "
-          f"max ncon {max(post['ncon'])}, mean iters {np.mean(post['solver_iter']):.2f}, "
+          f"max ncon {max(post['ncon'])}, robot-robot contacts {nself}, mean iters {np.mean(post['solver_iter']):.2f}, "
           f"healthy frac {np.mean(post['healthy']):.2f}")
     return out
 
@@ -117,6 +121,15 @@ def random_start(env, rng, kind):
         d.qpos[2] = rng.uniform(0.25, 0.4)
         d.qpos[7:] = np.where(rng.random(12) < 0.5, jr[:, 0] + 0.01, jr[:, 1] - 0.01)
         d.qvel[6:] = rng.normal(size=12) * 3
+    elif kind == "folded":       # knees fully folded, hips abducted inwards, legs crossing: robot-robot contacts from the first step
+        d.qpos[2] = rng.uniform(0.12, 0.3)
+        e = rng.uniform(-0.8, 0.8, size=3)
+        q = np.array([1.0, *(0.5 * e)]); d.qpos[3:7] = q / np.linalg.norm(q)
+        lo, hi = jr[:, 0], jr[:, 1]
+        u = rng.random(12)
+        d.qpos[7:] = lo + (hi - lo) * np.where(np.arange(12) % 3 == 2, 0.06 * u, u)      # knees near their lower limit
+        d.qpos[7::3] = np.array([1, -1, 1, -1]) * rng.uniform(0.4, 0.86, size=4)           # abduction towards the body
+        d.qvel[:] = rng.normal(size=18) * 0.5
     elif kind == "tilted":
         d.qpos[2] = rng.uniform(0.25, 0.35)
         e = rng.uniform(-0.6, 0.6, size=3)
@@ -157,7 +170,7 @@ def main():
         np.savez_compressed(os.path.join(OUT, f"trace_{ctrl}.npz"), **tr)
         # --- randomised starts
         chunks = []
-        for seed, kind in enumerate(("fallen", "airborne", "limits", "tilted", "fallen", "airborne"), start=1):
+        for seed, kind in enumerate(("fallen", "airborne", "limits", "tilted", "fallen", "airborne", "folded", "folded"), start=1):
             rng = np.random.default_rng(seed)
             random_start(env, rng, kind)
             chunks.append(record_trace(env, sample_actions(env, rng, 120), f"start seed {seed} ({kind})"))

@@ -44,7 +44,8 @@ extern "C" {
 #define GO1_NBODY 14
 #define GO1_INFO_DIM 16
 #define GO1_BIPED_INFO_DIM 12
-#define GO1_MAX_CONTACTS 64
+#define GO1_MAX_CONTACTS 40        /* contacts kept per environment and substep (floor + robot-robot); more are dropped and counted */
+#define GO1_MAX_PAIR_CONTACTS 8    /* robot-robot contacts among them */
 
 enum {
     GO1_OK = 0,
@@ -119,11 +120,13 @@ typedef struct Go1Diag {
 } Go1Diag;
 
 typedef struct Go1Contact {
-    int32_t geom;        /* MuJoCo geom id of the robot geom (geom1 is always the floor) */
+    int32_t geom;        /* mjContact.geom2: MuJoCo geom id of the robot geom */
     int32_t dim;
     double dist;
     double pos[3];       /* world */
     double force[6];     /* contact-frame force: normal, 2 tangents, torsion, 2 rolling */
+    int32_t geom1;       /* mjContact.geom1: 0 = the floor plane, otherwise the robot geom of the lower geom type (robot-robot contact) */
+    int32_t pad_;
 } Go1Contact;
 
 typedef struct Go1Stats {
@@ -135,7 +138,12 @@ typedef struct Go1Stats {
     double n_truncated;
     double n_bad_state;
     double env_steps;
+    double n_contact_overflow;     /* contacts dropped because an environment had more than GO1_MAX_CONTACTS (or GO1_MAX_PAIR_CONTACTS robot-robot) */
+    double sum_contacts;           /* active contacts in the last substep, summed over env-steps */
+    double sum_solver_iterations;  /* Newton iterations, summed over substeps and env-steps */
+    double sum_self_contacts;      /* robot-robot contacts in the last substep, summed over env-steps */
 } Go1Stats;
+#define GO1_NSTATS 12
 
 /* Policy for go1_rollout(action_mode=GO1_ACTION_POLICY): SB3 MlpPolicy actor 48-64-64-12 (tanh),
  * a = clip(mu + exp(log_std) * eps, low, high). Row-major [out][in] weights (torch layout), device ptrs. */

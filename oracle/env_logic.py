@@ -106,6 +106,19 @@ class EpisodeState:
     front_feet_touched: bool = False                                   # biped only (:476-479)
 
 
+def count_self_collisions(contacts, geom_bodyid):
+    """``self_collision_cost`` before its weight (go1_mujoco_env.py:269-312): contacts of ``data.contact`` between the
+    front-right and the front-left limb (bodies FR_hip/thigh/calf = 2..4, FL = 5..7) or between the rear pair (RR = 8..10,
+    RL = 11..13), in either geom order."""
+    fr, fl, rr, rl = {2, 3, 4}, {5, 6, 7}, {8, 9, 10}, {11, 12, 13}
+    n = 0
+    for c in contacts:
+        b1, b2 = int(geom_bodyid[c.geom1]), int(geom_bodyid[c.geom2])
+        if (b1 in fr and b2 in fl) or (b2 in fr and b1 in fl) or (b1 in rr and b2 in rl) or (b2 in rr and b1 in rl):
+            n += 1
+    return n
+
+
 class EnvLogic:
     """Per-step env logic given the physics results of ``do_simulation``."""
 

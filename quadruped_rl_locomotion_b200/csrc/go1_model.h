@@ -17,7 +17,9 @@ namespace go1 {
 constexpr int NLEG = 4;       // lanes per environment: one lane per leg
 constexpr int GMAX = 12;      // collision geoms handled by one lane (its leg's + a share of the trunk's)
 constexpr int CMAX = 16;      // active contacts kept per lane
-constexpr int NCLS = 4;       // distinct floor-contact parameter classes
+constexpr int NCLS = 8;       // distinct contact parameter classes (floor-mixed + robot-robot mixed)
+constexpr int NKIND = 4;      // distinct per-geom contact parameter sets
+constexpr int NBP = 72;       // body pairs that may collide (not parent and child, not hip-hip)
 constexpr int GFLAT = 44;     // robot collision geoms (flat list, sorted by body)
 
 // index tables of the block-arrow layout tt[21] | tk[4][6][3] | kk[4][6]  (go1_warp.cuh)
@@ -28,7 +30,8 @@ enum { G_SPHERE = 2, G_CAPSULE = 3, G_CYLINDER = 5, G_BOX = 6 };
 
 template <typename T>
 struct DevGeom {
-    int type, slot, cls, gid;  // slot: 0 trunk, 1..3 hip/thigh/calf of the lane's leg; gid: MuJoCo geom id
+    int type, slot, cls, gid;  // slot: body index (0 trunk, 1 + 3*leg + link); cls: class of the contact with the floor; gid: MuJoCo geom id
+    int kind, pad;             // kind: index of this geom's own contact parameter set (robot-robot classes: DevModel::pair_cls)
     T pos[3], zax[3], xax[3], size[3];
 };
 
@@ -66,6 +69,14 @@ struct DevModel {
     DevGeom<T> flat[GFLAT];
     T flat_rb[GFLAT];
     ArrowTab tab;
+    // robot-robot collision (mj_collision body pairs; go1_pair.cuh): flat-geom range and bounding sphere per body, body pairs in
+    // (body1, body2) order, class of a contact between geoms of kinds (a, b)
+    int body_g0[16];
+    T bsph[13][4];
+    int npairs, pair_margin_pad;
+    unsigned char pair_a[NBP], pair_b[NBP];
+    int pair_cls[NKIND][NKIND];
+    T pair_margin;
     // env constants
     T key_qpos[19], key_ctrl[12], soft_lo[12], soft_hi[12], ctrl_lo[12], ctrl_hi[12];
 };
@@ -279,6 +290,67 @@ inline bool build_dev_model(const void* data, size_t nbytes, DevModel<double>& M
         for (int c = 0; c < 9; c++) M.plane_frame[c] = f[c];
     }
     // ---- collision geoms -> lanes; contact parameter classes (mixing with the floor, mj_contactParam rules)
+    // contact parameter class of a geom pair (mj_contactParam rules) -> index into M.cls (created on first use)
+    std::string class_err;
+    auto class_of = [&](int ga, int gb) -> int {
+        DevClass<double> C;
+        std::memset(&C, 0, sizeof(C));
+        double fri[3], solref[2], solimp[5];
+        int p1 = geom_priority[ga], p2 = geom_priority[gb];
+        if (p1 != p2) {
+            int w = p1 > p2 ? ga : gb;
+            C.dim = geom_condim[w];
+            for (int c = 0; c < 3; c++) fri[c] = geom_friction[3 * w + c];
+            for (int c = 0; c < 2; c++) solref[c] = geom_solref[2 * w + c];
+            for (int c = 0; c < 5; c++) solimp[c] = geom_solimp[5 * w + c];
+        } else {
+            C.dim = geom_condim[ga] > geom_condim[gb] ? geom_condim[ga] : geom_condim[gb];
+            for (int c = 0; c < 3; c++) fri[c] = std::fmax(geom_friction[3 * ga + c], geom_friction[3 * gb + c]);
+            double m1 = geom_solmix[ga], m2 = geom_solmix[gb], mix;
+            if (m1 >= 1e-15 && m2 >= 1e-15) mix = m1 / (m1 + m2);
+            else if (m1 < 1e-15 && m2 < 1e-15) mix = 0.5;
+            else mix = m1 < 1e-15 ? 0.0 : 1.0;
+            for (int c = 0; c < 2; c++) solref[c] = mix * geom_solref[2 * ga + c] + (1 - mix) * geom_solref[2 * gb + c];
+            for (int c = 0; c < 5; c++) solimp[c] = mix * geom_solimp[5 * ga + c] + (1 - mix) * geom_solimp[5 * gb + c];
+        }
+        if (!(C.dim == 1 || C.dim == 3 || C.dim == 6)) { class_err = "contacts must have condim 1, 3 or 6 after mixing"; return -1; }
+        if (!(solref[0] > 0)) { class_err = "direct (negative) solref is not implemented"; return -1; }
+        C.fri[0] = C.fri[1] = std::fmax(1e-5, fri[0]); C.fri[2] = std::fmax(1e-5, fri[1]);
+        C.fri[3] = C.fri[4] = std::fmax(1e-5, fri[2]);
+        C.mu = C.fri[0] / std::sqrt(std::fmax(1e-15, M.impratio));
+        C.drat[0] = 1;
+        for (int jj = 1; jj < 6; jj++) C.drat[jj] = jj < C.dim ? M.impratio * C.fri[jj - 1] * C.fri[jj - 1] / (C.fri[0] * C.fri[0]) : 0.0;
+        C.d0 = std::fmin(0.9999, std::fmax(0.0001, solimp[0])); C.d1 = std::fmin(0.9999, std::fmax(0.0001, solimp[1]));
+        C.width = std::fmax(0.0, solimp[2]); C.mid = std::fmin(0.9999, std::fmax(0.0001, solimp[3])); C.power = std::fmax(1.0, solimp[4]);
+        double tc = std::fmax(solref[0], 2 * M.timestep);
+        C.K = 1 / std::fmax(1e-15, C.d1 * C.d1 * tc * tc * solref[1] * solref[1]);
+        C.B = 2 / std::fmax(1e-15, C.d1 * tc);
+        C.margin = std::fmax(geom_margin[ga], geom_margin[gb]);
+        C.incmargin = C.margin - std::fmax(geom_gap[ga], geom_gap[gb]);
+        for (int c = 0; c < M.nclass; c++) {
+            DevClass<double> a = M.cls[c];
+            if (std::memcmp(&a, &C, sizeof(C)) == 0) return c;
+        }
+        if (M.nclass >= NCLS) { class_err = "too many distinct contact parameter classes"; return -1; }
+        M.cls[M.nclass] = C;
+        return M.nclass++;
+    };
+    // per-geom contact parameter set ("kind"): geoms with identical own parameters share one
+    std::vector<int> kind_rep;
+    auto same_params = [&](int a, int b) {
+        bool eq = geom_priority[a] == geom_priority[b] && geom_condim[a] == geom_condim[b] && geom_solmix[a] == geom_solmix[b] &&
+                  geom_margin[a] == geom_margin[b] && geom_gap[a] == geom_gap[b];
+        for (int c = 0; c < 3; c++) eq = eq && geom_friction[3 * a + c] == geom_friction[3 * b + c];
+        for (int c = 0; c < 2; c++) eq = eq && geom_solref[2 * a + c] == geom_solref[2 * b + c];
+        for (int c = 0; c < 5; c++) eq = eq && geom_solimp[5 * a + c] == geom_solimp[5 * b + c];
+        return eq;
+    };
+    auto kind_of = [&](int g) -> int {
+        for (size_t k = 0; k < kind_rep.size(); k++) if (same_params(kind_rep[k], g)) return (int)k;
+        if ((int)kind_rep.size() >= NKIND) return -1;
+        kind_rep.push_back(g);
+        return (int)kind_rep.size() - 1;
+    };
     int trunk_share = 0;
     int cnt[NLEG][4];
     std::memset(cnt, 0, sizeof(cnt));
@@ -305,51 +377,11 @@ inline bool build_dev_model(const void* data, size_t nbytes, DevModel<double>& M
             dg.pos[c] = geom_pos[3 * g + c]; dg.size[c] = geom_size[3 * g + c];
             dg.zax[c] = R[3 * c + 2]; dg.xax[c] = R[3 * c + 0];
         }
-        // mix with the floor
-        DevClass<double> C;
-        std::memset(&C, 0, sizeof(C));
-        double fri[3], solref[2], solimp[5];
-        int p1 = geom_priority[floor], p2 = geom_priority[g];
-        if (p1 != p2) {
-            int w = p1 > p2 ? floor : g;
-            C.dim = geom_condim[w];
-            for (int c = 0; c < 3; c++) fri[c] = geom_friction[3 * w + c];
-            for (int c = 0; c < 2; c++) solref[c] = geom_solref[2 * w + c];
-            for (int c = 0; c < 5; c++) solimp[c] = geom_solimp[5 * w + c];
-        } else {
-            C.dim = geom_condim[floor] > geom_condim[g] ? geom_condim[floor] : geom_condim[g];
-            for (int c = 0; c < 3; c++) fri[c] = std::fmax(geom_friction[3 * floor + c], geom_friction[3 * g + c]);
-            double m1 = geom_solmix[floor], m2 = geom_solmix[g], mix;
-            if (m1 >= 1e-15 && m2 >= 1e-15) mix = m1 / (m1 + m2);
-            else if (m1 < 1e-15 && m2 < 1e-15) mix = 0.5;
-            else mix = m1 < 1e-15 ? 0.0 : 1.0;
-            for (int c = 0; c < 2; c++) solref[c] = mix * geom_solref[2 * floor + c] + (1 - mix) * geom_solref[2 * g + c];
-            for (int c = 0; c < 5; c++) solimp[c] = mix * geom_solimp[5 * floor + c] + (1 - mix) * geom_solimp[5 * g + c];
-        }
-        GO1_REQ(C.dim == 3 || C.dim == 6, "floor contacts must have condim 3 or 6 after mixing");
-        GO1_REQ(solref[0] > 0, "direct (negative) solref is not implemented");
-        C.fri[0] = C.fri[1] = std::fmax(1e-5, fri[0]); C.fri[2] = std::fmax(1e-5, fri[1]);
-        C.fri[3] = C.fri[4] = std::fmax(1e-5, fri[2]);
-        C.mu = C.fri[0] / std::sqrt(std::fmax(1e-15, M.impratio));
-        C.drat[0] = 1;
-        for (int jj = 1; jj < 6; jj++) C.drat[jj] = M.impratio * C.fri[jj - 1] * C.fri[jj - 1] / (C.fri[0] * C.fri[0]);
-        C.d0 = std::fmin(0.9999, std::fmax(0.0001, solimp[0])); C.d1 = std::fmin(0.9999, std::fmax(0.0001, solimp[1]));
-        C.width = std::fmax(0.0, solimp[2]); C.mid = std::fmin(0.9999, std::fmax(0.0001, solimp[3])); C.power = std::fmax(1.0, solimp[4]);
-        double tc = std::fmax(solref[0], 2 * M.timestep);
-        C.K = 1 / std::fmax(1e-15, C.d1 * C.d1 * tc * tc * solref[1] * solref[1]);
-        C.B = 2 / std::fmax(1e-15, C.d1 * tc);
-        C.margin = std::fmax(geom_margin[floor], geom_margin[g]);
-        C.incmargin = C.margin - std::fmax(geom_gap[floor], geom_gap[g]);
-        int ci = -1;
-        for (int c = 0; c < M.nclass; c++) {
-            DevClass<double> a = M.cls[c];
-            if (std::memcmp(&a, &C, sizeof(C)) == 0) ci = c;
-        }
-        if (ci < 0) {
-            GO1_REQ(M.nclass < NCLS, "too many distinct floor-contact parameter classes");
-            ci = M.nclass;
-            M.cls[M.nclass++] = C;
-        }
+        dg.kind = kind_of(g);
+        GO1_REQ(dg.kind >= 0, "too many distinct per-geom contact parameter sets");
+        int ci = class_of(floor, g);
+        GO1_REQ(ci >= 0, class_err.c_str());
+        GO1_REQ(M.cls[ci].dim == 3 || M.cls[ci].dim == 6, "floor contacts must have condim 3 or 6 after mixing");
         dg.cls = ci;
         tmp[lane][slot].push_back(dg);
     }
@@ -378,6 +410,51 @@ inline bool build_dev_model(const void* data, size_t nbytes, DevModel<double>& M
             for (int s = 1; s < 4; s++)
                 for (auto& dg : tmp[k][s]) GO1_REQ(push(dg, 1 + 3 * k + (s - 1)), "too many collision geoms");
         M.nflat = n;
+    }
+    // ---- robot-robot collision tables (mj_collision: body pairs that are not parent and child; geoms of one body never collide)
+    {
+        for (int b = 0; b <= 13; b++) {
+            int g = 0;
+            while (g < M.nflat && M.flat[g].slot < b) g++;
+            M.body_g0[b] = g;
+        }
+        M.body_g0[14] = M.body_g0[15] = M.nflat;
+        for (int b = 0; b < 13; b++) {
+            const int g0 = M.body_g0[b], g1 = M.body_g0[b + 1];
+            double c[3] = {0, 0, 0}, r = 0;
+            for (int g = g0; g < g1; g++) for (int k = 0; k < 3; k++) c[k] += M.flat[g].pos[k] / (g1 - g0);
+            for (int g = g0; g < g1; g++) {
+                double d2 = 0;
+                for (int k = 0; k < 3; k++) d2 += (M.flat[g].pos[k] - c[k]) * (M.flat[g].pos[k] - c[k]);
+                r = std::fmax(r, std::sqrt(d2) + M.flat_rb[g]);
+            }
+            for (int k = 0; k < 3; k++) M.bsph[b][k] = c[k];
+            M.bsph[b][3] = g1 > g0 ? r * (1 + 1e-6) : -1.0;
+        }
+        auto parent = [](int b) { return b == 0 ? -1 : ((b - 1) % 3 == 0 ? 0 : b - 1); };
+        auto only_cyl = [&](int b) { for (int g = M.body_g0[b]; g < M.body_g0[b + 1]; g++) if (M.flat[g].type != G_CYLINDER) return false; return true; };
+        M.npairs = 0;
+        M.pair_margin = 0;
+        for (int a = 0; a < 13; a++)
+            for (int b = a + 1; b < 13; b++) {
+                if (parent(b) == a || parent(a) == b) continue;
+                if (M.body_g0[a + 1] == M.body_g0[a] || M.body_g0[b + 1] == M.body_g0[b]) continue;
+                // cylinder-cylinder (hip motor vs hip motor; MuJoCo: MPR) is not collided: DESIGN.md states the reach of that pair
+                if (only_cyl(a) && only_cyl(b)) continue;
+                GO1_REQ((M.body_g0[a + 1] - M.body_g0[a]) * (M.body_g0[b + 1] - M.body_g0[b]) <= 32, "more than 32 geom pairs in one body pair");
+                GO1_REQ(M.npairs < NBP, "too many colliding body pairs");
+                M.pair_a[M.npairs] = (unsigned char)a; M.pair_b[M.npairs] = (unsigned char)b; M.npairs++;
+            }
+        for (int ka = 0; ka < NKIND; ka++)
+            for (int kb = 0; kb < NKIND; kb++) {
+                M.pair_cls[ka][kb] = 0;
+                if (ka < (int)kind_rep.size() && kb < (int)kind_rep.size()) {
+                    int ci = class_of(kind_rep[ka], kind_rep[kb]);
+                    GO1_REQ(ci >= 0, class_err.c_str());
+                    M.pair_cls[ka][kb] = ci;
+                    M.pair_margin = std::fmax(M.pair_margin, M.cls[ci].margin);
+                }
+            }
     }
     // block-arrow index tables
     {
@@ -432,9 +509,10 @@ inline void cast_dev_model(const DevModel<double>& S, DevModel<T>& D) {
     CPA(act_gear); CPA(act_gain); CPA(act_b0); CPA(act_b1); CPA(act_b2); CPA(act_clo); CPA(act_chi); CPA(act_flo); CPA(act_fhi);
     D.nflat = S.nflat;
     CPA(flat_rb); CPI(tab);
+    CPI(body_g0); CPA(bsph); D.npairs = S.npairs; CPI(pair_a); CPI(pair_b); CPI(pair_cls); CP(pair_margin);
     for (int g = 0; g < GFLAT; g++) {
         const DevGeom<double>& s = S.flat[g]; DevGeom<T>& d = D.flat[g];
-        d.type = s.type; d.slot = s.slot; d.cls = s.cls; d.gid = s.gid;
+        d.type = s.type; d.slot = s.slot; d.cls = s.cls; d.gid = s.gid; d.kind = s.kind;
         for (int c = 0; c < 3; c++) { d.pos[c] = (T)s.pos[c]; d.zax[c] = (T)s.zax[c]; d.xax[c] = (T)s.xax[c]; d.size[c] = (T)s.size[c]; }
     }
     for (int c = 0; c < NCLS; c++) {

@@ -50,7 +50,14 @@ constexpr int NDOF = 18;    // 0..5 trunk (3 lin world, 3 rot body frame), 6 + 3
 #ifndef GO1_CW
 #define GO1_CW 40
 #endif
+#ifndef GO1_SELF_COLLISION
+#define GO1_SELF_COLLISION 1   // robot-robot contacts (0: floor contacts only, the round-1 physics; timing A/B only)
+#endif
 constexpr int CW = GO1_CW;  // contacts kept per environment (geom order; the rest is counted as overflow)
+#ifndef GO1_PW
+#define GO1_PW 8
+#endif
+constexpr int PW = GO1_PW;  // robot-robot contacts kept per environment (stored after the floor contacts; both share the CW slots)
 constexpr int NARROW = 117; // block-arrow storage: tt[21] | tk[4][6][3] | kk[4][6]
 constexpr int A_TK = 21, A_KK = 93;
 
@@ -167,6 +174,10 @@ template <typename T> GO1_DEV T impedance(T d0, T d1, T width, T mid, T power, T
     return d0 + y * (d1 - d0);
 }
 
+}  // namespace go1
+#include "go1_pair.cuh"
+namespace go1 {
+
 // ---- per-environment shared-memory workspace (one per warp)
 template <typename T> struct WEnv {
     // persistent state row, same order as the global state slab (S_* offsets in go1sim.cu): 78 values + pad
@@ -185,15 +196,45 @@ template <typename T> struct WEnv {
     T cfrc[NB][6];                   // own contact wrench of every body about the COM (cfrc_ext of the last evaluation)
     T c_r[3][CW], c_D0[CW], c_aref[6][CW];
     T c_s[14][CW];                   // scratch: evaluate -> wrench(6) N T U1..U5 zone ; line search -> polynomial(11)
-    int c_meta[CW];                  // body | class << 8 | geom id << 16
-    int bstart[NB + 3];              // contacts of body b: [bstart[b], bstart[b+1])
-    int ncon, overflow;
+    T c_n[3][PW];                    // normal (geom1 -> geom2) of the robot-robot contacts [nfl, ncon)
+    int c_meta[CW];                  // body2 | (body1 + 1) << 4 (0: floor) | class << 8 | geom2 id << 16 | geom1 id << 22
+    int bstart[NB + 3];              // floor contacts of body b: [bstart[b], bstart[b+1])
+    int ncon, overflow, nfl, pad2_;  // nfl: floor contacts (sorted by body); [nfl, ncon): robot-robot contacts
     // aliases (lifetimes do not overlap, see DESIGN.md "shared-memory budget")
     GO1_DEV T (*xmat())[9] { return reinterpret_cast<T (*)[9]>(&Kc[0][0]); }
     GO1_DEV T (*xpos())[3] { return reinterpret_cast<T (*)[3]>(&Kc[0][0] + NB * 9); }
     GO1_DEV T (*ubuf())[6] { return reinterpret_cast<T (*)[6]>(&c_s[0][0]); }      // assemble_arrow scratch (c_s is dead then)
     GO1_DEV T (*wrench())[6] { return bv[1]; }
+    GO1_DEV T* kd() { return &Kc[0][0]; }              // dense 12x12 leg block of the Hessian (environments with leg-leg contacts)
+    GO1_DEV T* jbuf() { return &Kc[0][0] + 144; }      // 6 x 12 Jacobian rows of one robot-robot contact
 };
+
+GO1_DEV int meta_b2(int meta) { return meta & 15; }
+GO1_DEV int meta_b1p(int meta) { return (meta >> 4) & 15; }     // body1 + 1; 0 = the floor
+GO1_DEV int meta_cls(int meta) { return (meta >> 8) & 15; }
+
+// contact frame (rows: normal, two tangents): the floor's constant frame, or mju_makeFrame of the stored pair normal
+template <typename T> GO1_DEV void contact_frame(const DevModel<T>& m, const WEnv<T>& E, int c, int dim, T* F) {
+    if (c < E.nfl) {
+#pragma unroll
+        for (int e = 0; e < 9; e++) F[e] = m.plane_frame[e];
+    } else {
+        const int p = c - E.nfl;
+        F[0] = E.c_n[0][p]; F[1] = E.c_n[1][p]; F[2] = E.c_n[2][p];
+        if (dim > 1) make_frame_(F);
+        else { F[3] = F[4] = F[5] = F[6] = F[7] = F[8] = 0; }
+    }
+}
+// spatial motion of geom2's body relative to geom1's body (the floor does not move)
+template <typename T> GO1_DEV void contact_image(const T (*bv)[6], int meta, T* A) {
+    const int b2 = meta_b2(meta), b1p = meta_b1p(meta);
+#pragma unroll
+    for (int e = 0; e < 6; e++) A[e] = bv[b2][e];
+    if (b1p) {
+#pragma unroll
+        for (int e = 0; e < 6; e++) A[e] -= bv[b1p - 1][e];
+    }
+}
 
 
 
@@ -323,6 +364,52 @@ template <typename T> GO1_NOINL T arrow_matvec(const WEnv<T>& E, const T* A, int
     return s;
 }
 
+// dense 6x6 Cholesky of the packed tt block (diagonals inverted), every lane redundantly in registers; lane 0 stores
+template <typename T> GO1_DEV void chol6(T* A, int lane) {
+    typedef Num<T> N;
+    T p[21];
+#pragma unroll
+    for (int e = 0; e < 21; e++) p[e] = A[e];
+    __syncwarp();
+#pragma unroll
+    for (int j = 0; j < 6; j++) {
+        T d = p[SYM(j, j)];
+#pragma unroll
+        for (int k = 0; k < j; k++) d -= p[SYM(j, k)] * p[SYM(j, k)];
+        const T inv = N::rsqrt_(N::max_(d, N::MINVAL));
+        p[SYM(j, j)] = inv;
+#pragma unroll
+        for (int i = j + 1; i < 6; i++) {
+            T s = p[SYM(i, j)];
+#pragma unroll
+            for (int k = 0; k < j; k++) s -= p[SYM(i, k)] * p[SYM(j, k)];
+            p[SYM(i, j)] = s * inv;
+        }
+    }
+    if (lane == 0) {
+#pragma unroll
+        for (int e = 0; e < 21; e++) A[e] = p[e];
+    }
+    __syncwarp();
+}
+// x <- (L L')^-1 x with the factor of chol6
+template <typename T> GO1_DEV void solve6(const T* F, T* x) {
+#pragma unroll
+    for (int i = 0; i < 6; i++) {
+        T s = x[i];
+#pragma unroll
+        for (int k = 0; k < i; k++) s -= F[SYM(i, k)] * x[k];
+        x[i] = s * F[SYM(i, i)];
+    }
+#pragma unroll
+    for (int i = 5; i >= 0; i--) {
+        T s = x[i];
+#pragma unroll
+        for (int k = i + 1; k < 6; k++) s -= F[SYM(k, i)] * x[k];
+        x[i] = s * F[SYM(i, i)];
+    }
+}
+
 // in-place Cholesky of the block-arrow A: kk[k] -> L_k (diagonals inverted), tk[k] -> Y_k = C_k L_k^-T,
 // tt -> Cholesky factor of the Schur complement (diagonals inverted)
 template <typename T> GO1_NOINL void arrow_factor(const DevModel<T>& m, T* A, int lane) {
@@ -358,31 +445,7 @@ template <typename T> GO1_NOINL void arrow_factor(const DevModel<T>& m, T* A, in
         A[lane] -= s;
     }
     __syncwarp();
-    // dense 6x6 Cholesky, every lane redundantly in registers; lane 0 stores
-    T p[21];
-#pragma unroll
-    for (int e = 0; e < 21; e++) p[e] = A[e];
-    __syncwarp();
-#pragma unroll
-    for (int j = 0; j < 6; j++) {
-        T d = p[SYM(j, j)];
-#pragma unroll
-        for (int k = 0; k < j; k++) d -= p[SYM(j, k)] * p[SYM(j, k)];
-        const T inv = N::rsqrt_(N::max_(d, N::MINVAL));
-        p[SYM(j, j)] = inv;
-#pragma unroll
-        for (int i = j + 1; i < 6; i++) {
-            T s = p[SYM(i, j)];
-#pragma unroll
-            for (int k = 0; k < j; k++) s -= p[SYM(i, k)] * p[SYM(j, k)];
-            p[SYM(i, j)] = s * inv;
-        }
-    }
-    if (lane == 0) {
-#pragma unroll
-        for (int e = 0; e < 21; e++) A[e] = p[e];
-    }
-    __syncwarp();
+    chol6(A, lane);
 }
 
 // solves A x = g with the factor F (arrow_factor); g/x are per-dof-lane register values
@@ -410,20 +473,7 @@ template <typename T> GO1_NOINL T arrow_solve(WEnv<T>& E, const T* F, T g, int l
     T x[6];
 #pragma unroll
     for (int i = 0; i < 6; i++) x[i] = E.xv[i];
-#pragma unroll
-    for (int i = 0; i < 6; i++) {
-        T s = x[i];
-#pragma unroll
-        for (int k = 0; k < i; k++) s -= F[SYM(i, k)] * x[k];
-        x[i] = s * F[SYM(i, i)];
-    }
-#pragma unroll
-    for (int i = 5; i >= 0; i--) {
-        T s = x[i];
-#pragma unroll
-        for (int k = i + 1; k < 6; k++) s -= F[SYM(k, i)] * x[k];
-        x[i] = s * F[SYM(i, i)];
-    }
+    solve6(F, x);
     __syncwarp();
     if (lane >= 6 && lane < NDOF) {
         const int k = (lane - 6) / 3, i = lane - 6 - 3 * k;
@@ -448,6 +498,99 @@ template <typename T> GO1_NOINL T arrow_solve(WEnv<T>& E, const T* F, T g, int l
     const T r = lane < NDOF ? E.xv[lane] : T(0);
     __syncwarp();
     return r;
+}
+
+
+// ---- environments with a leg-leg contact: the 12 x 12 leg block KD = E.kd() is dense (pair_hessian), the trunk block tt and the
+// couplings tk stay in the arrow storage A.  Same elimination order as arrow_factor: KD = L L' (in place, diagonals inverted),
+// tk -> Y = C L^-T, tt -> Cholesky factor of the Schur complement tt - Y Y'.
+template <typename T> GO1_NOINL void dense_factor(WEnv<T>& E, const DevModel<T>& m, T* A, int lane) {
+    typedef Num<T> N;
+    T* KD = E.kd();
+#pragma unroll 1
+    for (int c = 0; c < 12; c++) {
+        const T inv = N::rsqrt_(N::max_(KD[c * 12 + c], N::MINVAL));
+        T l = 0;
+        if (lane > c && lane < 12) l = KD[lane * 12 + c] * inv;
+        __syncwarp();
+        if (lane > c && lane < 12) KD[lane * 12 + c] = l;
+        if (lane == c) KD[c * 12 + c] = inv;
+        __syncwarp();
+        if (lane > c && lane < 12)
+            for (int s2 = c + 1; s2 <= lane; s2++) KD[lane * 12 + s2] -= l * KD[s2 * 12 + c];
+        __syncwarp();
+    }
+    if (lane < 6) {      // row `lane` of Y: forward substitution L y' = c'
+        T y[12];
+#pragma unroll
+        for (int c = 0; c < 12; c++) {
+            T v = A[A_TK + 18 * (c / 3) + 3 * lane + (c % 3)];
+#pragma unroll
+            for (int p = 0; p < c; p++) v -= y[p] * KD[c * 12 + p];
+            y[c] = v * KD[c * 12 + c];
+        }
+#pragma unroll
+        for (int c = 0; c < 12; c++) A[A_TK + 18 * (c / 3) + 3 * lane + (c % 3)] = y[c];
+    }
+    __syncwarp();
+    if (lane < 21) {
+        const int r = m.tab.sym_r[lane], c = m.tab.sym_c[lane];
+        T s = 0;
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            const T* yr = A + A_TK + 18 * k + 3 * r; const T* yc = A + A_TK + 18 * k + 3 * c;
+            s += yr[0] * yc[0] + yr[1] * yc[1] + yr[2] * yc[2];
+        }
+        A[lane] -= s;
+    }
+    __syncwarp();
+    chol6(A, lane);
+}
+
+// solves H x = g with the factor of dense_factor; g / x are per-dof-lane register values
+template <typename T> GO1_NOINL T dense_solve(WEnv<T>& E, const T* F, T g, int lane) {
+    const T* KD = E.kd();
+    const int r = lane - 6;
+    const bool leg = lane >= 6 && lane < NDOF;
+    T x = g;
+#pragma unroll 1
+    for (int c = 0; c < 12; c++) {           // z = L^-1 g_legs
+        const T zc = __shfl_sync(FULL, x, 6 + c) * KD[c * 12 + c];
+        if (leg && r == c) x = zc;
+        else if (leg && r > c) x -= KD[r * 12 + c] * zc;
+    }
+    if (lane < NDOF) E.xv[lane] = x;
+    __syncwarp();
+    if (lane < 6) {
+        T s = 0;
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            const T* y = F + A_TK + 18 * k + 3 * lane; const T* z = E.xv + 6 + 3 * k;
+            s += y[0] * z[0] + y[1] * z[1] + y[2] * z[2];
+        }
+        E.xv[lane] -= s;
+    }
+    __syncwarp();
+    T x6[6];
+#pragma unroll
+    for (int i = 0; i < 6; i++) x6[i] = E.xv[i];
+    solve6(F, x6);
+    if (leg) {
+        const int k = r / 3, i = r - 3 * k;
+#pragma unroll
+        for (int j = 0; j < 6; j++) x -= F[A_TK + 18 * k + 3 * j + i] * x6[j];
+    }
+#pragma unroll 1
+    for (int c = 11; c >= 0; c--) {          // w = L^-T z
+        const T wc = __shfl_sync(FULL, x, 6 + c) * KD[c * 12 + c];
+        if (leg && r == c) x = wc;
+        else if (leg && r < c) x -= KD[c * 12 + r] * wc;
+    }
+    __syncwarp();
+    T res = 0;
+    if (lane < 6) res = lane == 0 ? x6[0] : (lane == 1 ? x6[1] : (lane == 2 ? x6[2] : (lane == 3 ? x6[3] : (lane == 4 ? x6[4] : x6[5]))));
+    else if (leg) res = x;
+    return res;
 }
 
 
@@ -603,18 +746,16 @@ template <typename T>
 GO1_DEV T evaluate_rows(const DevModel<T>& m, WEnv<T>& E, int lane, T a, const DofRows<T>& dr, T& qfc, T& hdiag, T* frc_out) {
     typedef Num<T> N;
     T cost = 0;
-    const T* F = m.plane_frame;
     const int ncon = E.ncon;
 #pragma unroll 1
     for (int c = lane; c < ncon; c += 32) {
         const int meta = E.c_meta[c];
-        const int b = meta & 0xff;
-        const DevClass<T>& cl = m.cls[(meta >> 8) & 0xff];
+        const DevClass<T>& cl = m.cls[meta_cls(meta)];
         const int dim = cl.dim;
         const T r[3] = {E.c_r[0][c], E.c_r[1][c], E.c_r[2][c]};
-        T A[6];
-#pragma unroll
-        for (int e = 0; e < 6; e++) A[e] = E.bv[0][b][e];
+        T A[6], F[9];
+        contact_image(E.bv[0], meta, A);
+        contact_frame(m, E, c, dim, F);
         T g[3][3];
 #pragma unroll
         for (int j = 0; j < 3; j++) cross3(g[j], r, F + 3 * j);
@@ -625,6 +766,7 @@ GO1_DEV T evaluate_rows(const DevModel<T>& m, WEnv<T>& E, int lane, T a, const D
             jar[j] = dot3(g[j], A) + dot3(F + 3 * j, A + 3) - E.c_aref[j][c];
             D[j] = D0 * cl.drat[j];
         }
+        if (dim == 1) { jar[1] = 0; jar[2] = 0; }       // frictionless robot-robot contact: the normal row only (drat[1..] = 0)
         if (dim == 6) {
 #pragma unroll
             for (int j = 0; j < 3; j++) { jar[3 + j] = dot3(F + 3 * j, A) - E.c_aref[3 + j][c]; D[3 + j] = D0 * cl.drat[3 + j]; }
@@ -695,12 +837,19 @@ GO1_DEV T evaluate_rows(const DevModel<T>& m, WEnv<T>& E, int lane, T a, const D
         }
     }
     __syncwarp();
-    // per-body sums of the contact wrenches (contacts are sorted by body)
+    // per-body sums of the contact wrenches (floor contacts are sorted by body; a robot-robot contact pushes geom2's body
+    // with +w and geom1's body with -w, mj_rnePostConstraint)
+    const int nfl = E.nfl;
 #pragma unroll 1
     for (int idx = lane; idx < NB * 6; idx += 32) {
         const int b = idx / 6, e = idx - 6 * b;
         T s = 0;
         for (int c = E.bstart[b]; c < E.bstart[b + 1]; c++) s += E.c_s[e][c];
+        for (int c = nfl; c < ncon; c++) {
+            const int meta = E.c_meta[c];
+            if (meta_b2(meta) == b) s += E.c_s[e][c];
+            if (meta_b1p(meta) == b + 1) s -= E.c_s[e][c];
+        }
         E.wrench()[b][e] = s; E.cfrc[b][e] = s;
     }
     __syncwarp();
@@ -708,13 +857,40 @@ GO1_DEV T evaluate_rows(const DevModel<T>& m, WEnv<T>& E, int lane, T a, const D
     return cost;
 }
 
-// per-body contact stiffness K_b += G' Hc G for every contact in the bottom / middle zone (lanes e < 21 own one
-// entry of the packed symmetric 6x6).  Hc = diag(D) in the bottom zone; in the middle zone the cone Hessian
-// Dm*S*Hu*S (mj_constraintUpdate) is diagonal + rank 2:  sum_r w_r g_r g_r' + al (p q' + q p') + be q q'.
+// One entry gx' Hc gy of a contact's Hessian block (gx / gy: the 6 constraint-row values of two columns).  Hc = diag(D) in
+// the bottom zone; in the middle zone the cone Hessian Dm*S*Hu*S (mj_constraintUpdate) is diagonal + rank 2:
+// sum_r w_r g_r g_r' + al (p q' + q p') + be q q'.
+template <typename T>
+GO1_DEV T cone_quad(const DevClass<T>& cl, const WEnv<T>& E, int c, int zone, T D0, const T* gx, const T* gy) {
+    typedef Num<T> N;
+    T val = 0;
+    if (zone == 1) {
+#pragma unroll
+        for (int j = 0; j < 6; j++) val += D0 * cl.drat[j] * gx[j] * gy[j];     // rows >= dim: g = 0
+    } else {
+        const T mu = cl.mu;
+        const T Nn = E.c_s[6][c], Tt = E.c_s[7][c];
+        const T Dm = D0 / N::max_(mu * mu * (1 + mu * mu), N::MINVAL);
+        const T a1 = mu * Nn / (Tt * Tt * Tt), a2 = mu * mu - mu * Nn / Tt;
+        T qx = 0, qy = 0;
+        val = mu * mu * gx[0] * gy[0];
+#pragma unroll
+        for (int j = 1; j < 6; j++) {
+            const T sj = cl.fri[j - 1], Uj = E.c_s[7 + j][c];
+            qx += sj * Uj * gx[j]; qy += sj * Uj * gy[j];
+            val += a2 * sj * sj * gx[j] * gy[j];
+        }
+        val += (-mu * mu / Tt) * (gx[0] * qy + qx * gy[0]) + a1 * qx * qy;
+        val *= Dm;
+    }
+    return val;
+}
+
+// per-body contact stiffness K_b += G' Hc G for every FLOOR contact in the bottom / middle zone (lanes e < 21 own one
+// entry of the packed symmetric 6x6).  Robot-robot contacts couple two chains and are added by pair_hessian.
 template <typename T>
 GO1_DEV bool contact_stiffness(const DevModel<T>& m, WEnv<T>& E, int lane) {
-    typedef Num<T> N;
-    const int ncon = E.ncon;
+    const int ncon = E.nfl;
     bool any = false;
     for (int c = lane; c < ncon; c += 32) any |= E.c_s[13][c] != 0;
     if (!__any_sync(FULL, any)) return false;
@@ -729,8 +905,8 @@ GO1_DEV bool contact_stiffness(const DevModel<T>& m, WEnv<T>& E, int lane) {
         const int zone = (int)E.c_s[13][c];
         if (zone == 0) continue;
         const int meta = E.c_meta[c];
-        const int b = meta & 0xff;
-        const DevClass<T>& cl = m.cls[(meta >> 8) & 0xff];
+        const int b = meta_b2(meta);
+        const DevClass<T>& cl = m.cls[meta_cls(meta)];
         const int dim = cl.dim;
         const T D0 = E.c_D0[c];
         const T r[3] = {E.c_r[0][c], E.c_r[1][c], E.c_r[2][c]};
@@ -745,30 +921,87 @@ GO1_DEV bool contact_stiffness(const DevModel<T>& m, WEnv<T>& E, int lane) {
             gx[3 + j] = (dim == 6 && x < 3) ? F[3 * j + x] : T(0);
             gy[3 + j] = (dim == 6 && y < 3) ? F[3 * j + y] : T(0);
         }
-        T val = 0;
-        if (zone == 1) {
-#pragma unroll
-            for (int j = 0; j < 6; j++) val += D0 * cl.drat[j] * gx[j] * gy[j];     // rows >= dim: g = 0
-        } else {
-            const T mu = cl.mu;
-            const T Nn = E.c_s[6][c], Tt = E.c_s[7][c];
-            const T Dm = D0 / N::max_(mu * mu * (1 + mu * mu), N::MINVAL);
-            const T a1 = mu * Nn / (Tt * Tt * Tt), a2 = mu * mu - mu * Nn / Tt;
-            T qx = 0, qy = 0;
-            val = mu * mu * gx[0] * gy[0];
-#pragma unroll
-            for (int j = 1; j < 6; j++) {
-                const T sj = cl.fri[j - 1], Uj = E.c_s[7 + j][c];
-                qx += sj * Uj * gx[j]; qy += sj * Uj * gy[j];
-                val += a2 * sj * sj * gx[j] * gy[j];
-            }
-            val += (-mu * mu / Tt) * (gx[0] * qy + qx * gy[0]) + a1 * qx * qy;
-            val *= Dm;
-        }
+        const T val = cone_quad(cl, E, c, zone, D0, gx, gy);
         if (lane < 21) E.Kc[b][lane] += val;
     }
     __syncwarp();
     return true;
+}
+
+// Hessian terms of the robot-robot contacts in the bottom / middle zone.  Both bodies ride on the trunk, so the rows
+// J = G (S_body2 - S_body1) are zero on the six trunk dofs: the terms live in the 12 x 12 leg block.  Contacts within one
+// leg, or between a leg and the trunk, stay inside that leg's 3x3 block of the block-arrow matrix (return 1, added to
+// E.H).  A contact between two legs fills the off-diagonal 3x3 block: the leg block becomes dense (return 2, complete
+// 12 x 12 block in E.kd(); dense_factor / dense_solve).  Returns 0 when no such contact is active.  E.H must hold the arrow.
+template <typename T>
+GO1_NOINL int pair_hessian(const DevModel<T>& m, WEnv<T>& E, int lane) {
+    const int nfl = E.nfl, ncon = E.ncon;
+    bool any = false, cross = false;
+    for (int c = nfl + lane; c < ncon; c += 32) {
+        if (E.c_s[13][c] != 0) {
+            any = true;
+            const int meta = E.c_meta[c];
+            const int b2 = meta_b2(meta), b1 = meta_b1p(meta) - 1;
+            cross |= b1 >= 1 && b2 >= 1 && (b1 - 1) / 3 != (b2 - 1) / 3;
+        }
+    }
+    if (!__any_sync(FULL, any)) return 0;
+    const bool dense = __any_sync(FULL, cross);
+    T* KD = E.kd();
+    T* JB = E.jbuf();
+#pragma unroll 1
+    for (int idx = lane; idx < 144; idx += 32) KD[idx] = 0;
+    __syncwarp();
+#pragma unroll 1
+    for (int c = nfl; c < ncon; c++) {
+        const int zone = (int)E.c_s[13][c];
+        if (zone == 0) continue;
+        const int meta = E.c_meta[c];
+        const DevClass<T>& cl = m.cls[meta_cls(meta)];
+        const int dim = cl.dim;
+        if (lane < 12) {
+            const int b2 = meta_b2(meta), b1 = meta_b1p(meta) - 1;
+            const int k = lane / 3, i = lane - 3 * k;          // dof 6 + lane moves body b iff b is link >= i of leg k
+            const bool m2 = b2 >= 1 && (b2 - 1) / 3 == k && (b2 - 1) - 3 * k >= i;
+            const bool m1 = b1 >= 1 && (b1 - 1) / 3 == k && (b1 - 1) - 3 * k >= i;
+            const T sgn = (m2 ? T(1) : T(0)) - (m1 ? T(1) : T(0));
+            T F[9], cd[6];
+            contact_frame(m, E, c, dim, F);
+            const T r[3] = {E.c_r[0][c], E.c_r[1][c], E.c_r[2][c]};
+#pragma unroll
+            for (int e = 0; e < 6; e++) cd[e] = E.cdof[6 + lane][e];
+#pragma unroll
+            for (int j = 0; j < 3; j++) {
+                T cr[3];
+                cross3(cr, r, F + 3 * j);
+                JB[j * 12 + lane] = j < dim ? sgn * (dot3(cr, cd) + dot3(F + 3 * j, cd + 3)) : T(0);
+                JB[(3 + j) * 12 + lane] = dim == 6 ? sgn * dot3(F + 3 * j, cd) : T(0);
+            }
+        }
+        __syncwarp();
+        const T D0 = E.c_D0[c];
+#pragma unroll 1
+        for (int idx = lane; idx < 144; idx += 32) {
+            const int u = idx / 12, v = idx - 12 * u;
+            T gx[6], gy[6];
+#pragma unroll
+            for (int j = 0; j < 6; j++) { gx[j] = JB[j * 12 + u]; gy[j] = JB[j * 12 + v]; }
+            KD[idx] += cone_quad(cl, E, c, zone, D0, gx, gy);
+        }
+        __syncwarp();
+    }
+    if (lane < 24) {
+        const int k = lane / 6, e = lane - 6 * k;
+        const int i = m.tab.sym_r[e], cc = m.tab.sym_c[e];
+        if (!dense) E.H[A_KK + 6 * k + e] += KD[(3 * k + i) * 12 + 3 * k + cc];
+        else {
+            const T hv = E.H[A_KK + 6 * k + e];
+            KD[(3 * k + i) * 12 + 3 * k + cc] += hv;
+            if (i != cc) KD[(3 * k + cc) * 12 + 3 * k + i] += hv;
+        }
+    }
+    __syncwarp();
+    return dense ? 2 : 1;
 }
 
 // line-search polynomials of every contact for the direction whose body-space image is E.bv[1] (S), at the
@@ -776,18 +1009,17 @@ GO1_DEV bool contact_stiffness(const DevModel<T>& m, WEnv<T>& E, int lane) {
 template <typename T>
 GO1_DEV void ls_prepare(const DevModel<T>& m, WEnv<T>& E, int lane) {
     typedef Num<T> N;
-    const T* F = m.plane_frame;
     const int ncon = E.ncon;
 #pragma unroll 1
     for (int c = lane; c < ncon; c += 32) {
         const int meta = E.c_meta[c];
-        const int b = meta & 0xff;
-        const DevClass<T>& cl = m.cls[(meta >> 8) & 0xff];
+        const DevClass<T>& cl = m.cls[meta_cls(meta)];
         const int dim = cl.dim;
         const T r[3] = {E.c_r[0][c], E.c_r[1][c], E.c_r[2][c]};
-        T A[6], S[6];
-#pragma unroll
-        for (int e = 0; e < 6; e++) { A[e] = E.bv[0][b][e]; S[e] = E.bv[1][b][e]; }
+        T A[6], S[6], F[9];
+        contact_image(E.bv[0], meta, A);
+        contact_image(E.bv[1], meta, S);
+        contact_frame(m, E, c, dim, F);
         const T D0 = E.c_D0[c], mu = cl.mu;
         T q0 = 0, q1 = 0, q2 = 0, U0 = 0, V0 = 0, UU = 0, UV = 0, VV = 0;
 #pragma unroll
@@ -835,7 +1067,7 @@ GO1_NOINL LSPoint<T> ls_eval(const DevModel<T>& m, const WEnv<T>& E, int lane, T
     const int ncon = E.ncon;
 #pragma unroll 1
     for (int c = lane; c < ncon; c += 32) {
-        const DevClass<T>& cl = m.cls[(E.c_meta[c] >> 8) & 0xff];
+        const DevClass<T>& cl = m.cls[meta_cls(E.c_meta[c])];
         const T mu = cl.mu;
         const T q0 = E.c_s[0][c], q1 = E.c_s[1][c], q2 = E.c_s[2][c], q3 = E.c_s[3][c], q4 = E.c_s[4][c], q5 = E.c_s[5][c];
         const T q6 = E.c_s[6][c], q7 = E.c_s[7][c], T0 = E.c_s[8][c], x0 = E.c_s[10][c];
@@ -1073,14 +1305,100 @@ GO1_NOINL void substep_w(const DevModel<T>& m, const EnvCfg<T>& cfg, WEnv<T>& E,
             base += total;
         }
         __syncwarp();
-        if (lane == 0) { E.ncon = base < CW ? base : CW; E.overflow = base > CW ? base - CW : 0; }
-        const int ncon = base < CW ? base : CW;
-        // body ranges (contacts are sorted by body): bstart[b] = number of contacts with body < b
+        const int nfl = base < CW ? base : CW;
+        int nover = base > CW ? base - CW : 0;
+        // body ranges (floor contacts are sorted by body): bstart[b] = number of floor contacts with body < b
         if (lane <= NB) {
-            int lo = 0, hi = ncon;
-            while (lo < hi) { const int mid = (lo + hi) >> 1; if ((E.c_meta[mid] & 0xff) < lane) lo = mid + 1; else hi = mid; }
+            int lo = 0, hi = nfl;
+            while (lo < hi) { const int mid = (lo + hi) >> 1; if (meta_b2(E.c_meta[mid]) < lane) lo = mid + 1; else hi = mid; }
             E.bstart[lane] = lo;
         }
+        // ---- robot-robot pairs (mj_collision body pairs in (body1, body2) order; go1_pair.cuh).  The body frames are still in
+        // the Kc words; the centres of the bodies' bounding spheres go to the (dead) contact scratch.
+        int nall = nfl;
+#if GO1_SELF_COLLISION
+        {
+            T* bc = &E.c_s[0][0];
+            if (lane < NB) {
+                T cw[3];
+                matvec3(cw, E.xmat()[lane], m.bsph[lane]);
+#pragma unroll
+                for (int e = 0; e < 3; e++) bc[3 * lane + e] = cw[e] + E.xpos()[lane][e];
+            }
+            __syncwarp();
+            const T pmargin = m.pair_margin;
+#pragma unroll 1
+            for (int p0 = 0; p0 < m.npairs; p0 += 32) {
+                const int pi = p0 + lane;
+                bool hit = false;
+                if (pi < m.npairs) {
+                    const int a = m.pair_a[pi], b = m.pair_b[pi];
+                    const T d[3] = {bc[3 * a] - bc[3 * b], bc[3 * a + 1] - bc[3 * b + 1], bc[3 * a + 2] - bc[3 * b + 2]};
+                    const T bound = m.bsph[a][3] + m.bsph[b][3] + pmargin;
+                    hit = dot3(d, d) <= bound * bound;
+                }
+                unsigned mask = __ballot_sync(FULL, hit);
+#pragma unroll 1
+                while (mask) {
+                    const int pj = p0 + __ffs((int)mask) - 1;
+                    mask &= mask - 1;
+                    const int a = m.pair_a[pj], b = m.pair_b[pj];
+                    const int ga0 = m.body_g0[a], na = m.body_g0[a + 1] - ga0, gb0 = m.body_g0[b], nb = m.body_g0[b + 1] - gb0;
+                    Stage2<T> st;
+                    st.cnt = 0;
+#pragma unroll
+                    for (int k = 0; k < 3; k++) { st.p[0][k] = st.p[1][k] = st.n[0][k] = st.n[1][k] = 0; }
+                    st.d[0] = st.d[1] = 0;
+                    int meta = 0;
+                    if (lane < na * nb) {
+                        const int ia = lane / nb, ib = lane - ia * nb;
+                        int g1 = ga0 + ia, g2 = gb0 + ib;           // flat indices; geom1 = the lower geom type (mj_collideGeoms)
+                        if (m.flat[g1].type > m.flat[g2].type) { const int t_ = g1; g1 = g2; g2 = t_; }
+                        GeomW<T> w1, w2;
+#pragma unroll
+                        for (int q = 0; q < 2; q++) {
+                            const DevGeom<T>& g = m.flat[q == 0 ? g1 : g2];
+                            GeomW<T>& w = q == 0 ? w1 : w2;
+                            const T* Rg = E.xmat()[g.slot];
+                            w.type = g.type;
+                            matvec3(w.c, Rg, g.pos);
+                            matvec3(w.z, Rg, g.zax);
+                            matvec3(w.x, Rg, g.xax);
+#pragma unroll
+                            for (int k = 0; k < 3; k++) { w.c[k] += E.xpos()[g.slot][k]; w.s[k] = g.size[k]; }
+                        }
+                        const DevGeom<T>& G1 = m.flat[g1]; const DevGeom<T>& G2 = m.flat[g2];
+                        const int ci = m.pair_cls[G1.kind][G2.kind];
+                        const T margin = m.cls[ci].margin, inc = m.cls[ci].incmargin;
+                        const T dd[3] = {w2.c[0] - w1.c[0], w2.c[1] - w1.c[1], w2.c[2] - w1.c[2]};
+                        const T bound = m.flat_rb[g1] + m.flat_rb[g2] + margin;
+                        if (dot3(dd, dd) <= bound * bound) pp_collide(w1, w2, margin, inc, st);
+                        meta = G2.slot | ((G1.slot + 1) << 4) | (ci << 8) | (G2.gid << 16) | (G1.gid << 22);
+                    }
+                    int cnt = st.cnt < 2 ? st.cnt : 2;
+                    int incl = cnt;
+#pragma unroll
+                    for (int d = 1; d < 32; d <<= 1) { const int v = __shfl_up_sync(FULL, incl, d); if (lane >= d) incl += v; }
+                    const int total = __shfl_sync(FULL, incl, 31);
+                    const int off = nall + incl - cnt;
+#pragma unroll
+                    for (int j = 0; j < 2; j++) {
+                        const int c = off + j;
+                        if (j < cnt && c < CW && c - nfl < PW) {
+                            E.c_r[0][c] = st.p[j][0] - com[0]; E.c_r[1][c] = st.p[j][1] - com[1]; E.c_r[2][c] = st.p[j][2] - com[2];
+                            E.c_D0[c] = st.d[j]; E.c_meta[c] = meta;
+                            E.c_n[0][c - nfl] = st.n[j][0]; E.c_n[1][c - nfl] = st.n[j][1]; E.c_n[2][c - nfl] = st.n[j][2];
+                        }
+                    }
+                    nall += total;
+                }
+            }
+            int cap = nfl + PW < CW ? nfl + PW : CW;
+            if (nall > cap) { nover += nall - cap; nall = cap; }
+        }
+#endif
+        __syncwarp();
+        if (lane == 0) { E.ncon = nall; E.nfl = nfl; E.overflow = nover; }
         __syncwarp();
     }
     ncon = E.ncon;
@@ -1162,22 +1480,23 @@ GO1_NOINL void substep_w(const DevModel<T>& m, const EnvCfg<T>& cfg, WEnv<T>& E,
     as_ = arrow_solve(E, E.H, qfs, lane);
     // ------------------------------------------------------------------ contact rows: impedance, D, reference acceleration
     {
-        const T* F = m.plane_frame;
 #pragma unroll 1
         for (int c = lane; c < ncon; c += 32) {
             const int meta = E.c_meta[c];
-            const int b = meta & 0xff;
-            const DevClass<T>& cl = m.cls[(meta >> 8) & 0xff];
+            const int b = meta_b2(meta), b1p = meta_b1p(meta);
+            const DevClass<T>& cl = m.cls[meta_cls(meta)];
             const T dist = E.c_D0[c];
             const T pm = dist - cl.incmargin;
             const T imp = impedance(cl.d0, cl.d1, cl.width, cl.mid, cl.power, pm);
-            const T dA = (b == 0) ? m.t_invw[0] : (&m.invw[0][0][0])[2 * (b - 1)];
+            // mj_diagApprox: translational body_invweight0 of both bodies (the world's is 0)
+            T dA = (b == 0) ? m.t_invw[0] : (&m.invw[0][0][0])[2 * (b - 1)];
+            if (b1p) dA += (b1p == 1) ? m.t_invw[0] : (&m.invw[0][0][0])[2 * (b1p - 2)];
             const T Rr = N::max_(N::MINVAL, (1 - imp) * dA / imp);
             E.c_D0[c] = T(1) / Rr;
             const T r[3] = {E.c_r[0][c], E.c_r[1][c], E.c_r[2][c]};
-            T cv[6], vp[3];
-#pragma unroll
-            for (int e = 0; e < 6; e++) cv[e] = E.bv[0][b][e];
+            T cv[6], vp[3], F[9];
+            contact_image(E.bv[0], meta, cv);
+            contact_frame(m, E, c, cl.dim, F);
             cross3(vp, cv, r);
             vp[0] += cv[3]; vp[1] += cv[4]; vp[2] += cv[5];
 #pragma unroll
@@ -1301,8 +1620,16 @@ GO1_NOINL void substep_w(const DevModel<T>& m, const EnvCfg<T>& cfg, WEnv<T>& E,
             if (legdof) { const int k = jl / 3, i = jl - 3 * k; E.H[A_KK + 6 * k + SYM(i, i)] += hdiag; }
         }
         __syncwarp();
-        arrow_factor(m, E.H, lane);
-        const T s = -arrow_solve(E, E.H, grad, lane);
+        // robot-robot contacts (rare): inside one leg block, or leg-leg fill -> dense 12 x 12 leg block
+        const int pmode = E.ncon > E.nfl ? pair_hessian(m, E, lane) : 0;
+        T s;
+        if (pmode == 2) {
+            dense_factor(E, m, E.H, lane);
+            s = -dense_solve(E, E.H, grad, lane);
+        } else {
+            arrow_factor(m, E.H, lane);
+            s = -arrow_solve(E, E.H, grad, lane);
+        }
         // Newton decrement: -g.s/2 is the improvement the quadratic model predicts for the move about to be made.  If it
         // is below the tolerance, MuJoCo would make the move, measure "improvement < tolerance" and stop; stopping here
         // reaches the same optimum to within the same tolerance and skips that line search and the extra evaluation

@@ -25,6 +25,8 @@
 #include "../../include/go1sim.h"
 #include "go1_warp.cuh"
 
+static_assert(go1::CW == GO1_MAX_CONTACTS && go1::PW == GO1_MAX_PAIR_CONTACTS, "include/go1sim.h capacities must match the kernel build");
+
 #ifndef GO1_REAL
 #define GO1_REAL float
 #endif
@@ -64,7 +66,7 @@ struct KParams {
     float* obs; float* rew; uint8_t* done; uint8_t* trunc; float* term_obs; float* info;
     T* diag; int* diag_i; T* diag_con;   // nullable
     T* bipk; float* bip_info;      // biped mode only: [N][BK_N] kinematic snapshot, [N][GO1_BIPED_INFO_DIM] reward_info terms
-    double* stats;                 // nullable: 8 doubles
+    double* stats;                 // nullable: GO1_NSTATS doubles
     int* queue;                    // environment queue head (zeroed before every launch)
     const int* order;              // queue position -> environment (sorted by last step's solver work)
     int* work;                     // per environment: Newton iterations of this control step
@@ -212,7 +214,7 @@ __global__ void __launch_bounds__(GO1_WARPS * 32, GO1_MINBLOCKS) k_step(const __
     const EnvCfg<T>& cfg = P.cfg;
     const int N = P.n_envs;
     typedef Num<T> NN;
-    double st_acc = 0;     // lane i < 8: i-th rollout statistic summed over the environments this warp stepped
+    double st_acc = 0;     // lane i < GO1_NSTATS: i-th rollout statistic summed over the environments this warp stepped
     // persistent blocks: the block pulls the next GO1_WARPS environments from a global queue until the slab is done
     __shared__ int s_base;
     for (;;) {
@@ -279,7 +281,7 @@ __global__ void __launch_bounds__(GO1_WARPS * 32, GO1_MINBLOCKS) k_step(const __
             if (out.bad) {   // mjData of a skipped step: nothing the reward code may read is left uninitialised
                 for (int i = lane; i < NB * 6; i += 32) (&E.cfrc[0][0])[i] = 0;
                 if (lane < 3) E.com[lane] = 0;
-                if (lane == 0) { E.ncon = 0; E.overflow = 0; }
+                if (lane == 0) { E.ncon = 0; E.nfl = 0; E.overflow = 0; }
                 __syncwarp();
             }
             for (int s = 0; s < cfg.frame_skip; s++) {
@@ -416,7 +418,20 @@ __global__ void __launch_bounds__(GO1_WARPS * 32, GO1_MINBLOCKS) k_step(const __
                 bterm[6] = (d0 * d0 + d1 * d1) * bw[6];                                                         // :354-376
                 bterm[7] = s_ab * bw[7];
                 bterm[8] = s_uc * bw[8];
-                bterm[9] = T(0) * bw[9];      // :269-312 counts robot-robot contacts, which are not generated
+                // :269-312 self_collision_cost: contacts between the front-right and front-left limbs, or rear-right and rear-left
+                // (hip, thigh, calf of legs FR 0 / FL 1 / RR 2 / RL 3), counted over data.contact of the last substep
+                int nself = 0;
+                if (!out.bad)
+                    for (int c = E.nfl + lane; c < E.ncon; c += 32) {
+                        const int mt = E.c_meta[c];
+                        const int b2 = meta_b2(mt), b1 = meta_b1p(mt) - 1;
+                        if (b1 >= 1 && b2 >= 1) {
+                            const int l1 = (b1 - 1) / 3, l2 = (b2 - 1) / 3;
+                            nself += ((l1 ^ l2) == 1 && (l1 >> 1) == (l2 >> 1)) ? 1 : 0;
+                        }
+                    }
+                nself = warp_sum(nself);
+                bterm[9] = T(nself) * bw[9];
                 rewards += bterm[0];
 #pragma unroll
                 for (int i = 1; i < 10; i++) costs += bterm[i];
@@ -498,6 +513,10 @@ __global__ void __launch_bounds__(GO1_WARPS * 32, GO1_MINBLOCKS) k_step(const __
                 else if (lane == 5) v = (truncated && !terminated) ? 1.0 : 0.0;
                 else if (lane == 6) v = nonfinite ? 1.0 : 0.0;
                 else if (lane == 7) v = 1.0;
+                else if (lane == 8) v = (double)out.overflow;                 // contacts dropped for lack of slots (summed over substeps)
+                else if (lane == 9) v = (double)out.ncon;                      // active contacts, last substep
+                else if (lane == 10) v = (double)out.iters_total;              // Newton iterations of the control step
+                else if (lane == 11) v = out.bad ? 0.0 : (double)(E.ncon - E.nfl);   // robot-robot contacts, last substep
                 st_acc += v;
             }
             if (done) {
@@ -508,7 +527,7 @@ __global__ void __launch_bounds__(GO1_WARPS * 32, GO1_MINBLOCKS) k_step(const __
             store_state();
         }
     }
-    if (P.stats && lane < 8 && st_acc != 0.0) atomicAdd(P.stats + lane, st_acc);
+    if (P.stats && lane < GO1_NSTATS && st_acc != 0.0) atomicAdd(P.stats + lane, st_acc);
 }
 
 // Queue order for the next control step: environments sorted by the solver work of the last one (counting sort,
@@ -690,7 +709,7 @@ int go1_create(const void* model_blob, size_t nbytes, const Go1EnvConfig* cfg_in
     const size_t N = (size_t)n_envs;
 #define ALLOC(p, bytes) if ((e = cudaMalloc((void**)&(p), (bytes))) != cudaSuccess) return fail("cudaMalloc " #p, e); cudaMemset((p), 0, (bytes))
     ALLOC(h->sreal, sizeof(real) * S_STRIDE * N); ALLOC(h->sint, sizeof(int) * I_STRIDE * N);
-    ALLOC(h->stats, sizeof(double) * 8); ALLOC(h->queue, sizeof(int) * 4); ALLOC(h->order, sizeof(int) * N); ALLOC(h->work, sizeof(int) * N);
+    ALLOC(h->stats, sizeof(double) * GO1_NSTATS); ALLOC(h->queue, sizeof(int) * 4); ALLOC(h->order, sizeof(int) * N); ALLOC(h->work, sizeof(int) * N);
     ALLOC(h->d_act, sizeof(float) * 12 * N); ALLOC(h->d_obs, sizeof(float) * 48 * N); ALLOC(h->d_rew, sizeof(float) * N);
     ALLOC(h->d_tobs, sizeof(float) * 48 * N); ALLOC(h->d_info, sizeof(float) * GO1_INFO_DIM * N);
     ALLOC(h->d_done, N); ALLOC(h->d_trunc, N); ALLOC(h->d_mask, N);
@@ -893,7 +912,7 @@ int go1_rollout(go1_handle h, int n_steps, int action_mode, const Go1Policy* pol
     if (action_mode == GO1_ACTION_POLICY && !policy) { h->err = "go1_rollout: policy mode needs a policy"; return GO1_EINVAL; }
     CK(cudaSetDevice(h->device));
     cudaStream_t s = stream ? (cudaStream_t)stream : h->stream;
-    CK(cudaMemsetAsync(h->stats, 0, sizeof(double) * 8, s));
+    CK(cudaMemsetAsync(h->stats, 0, sizeof(double) * GO1_NSTATS, s));
     int launches = 0;
     CK(cudaEventRecord(h->ev0, s));
     for (int t = 0; t < n_steps; t++) {
@@ -923,10 +942,11 @@ int go1_rollout(go1_handle h, int n_steps, int action_mode, const Go1Policy* pol
     CK(cudaEventElapsedTime(&h->last_ms, h->ev0, h->ev1));
     h->last_launches = launches;
     if (out) {
-        double st[8];
+        double st[GO1_NSTATS];
         CK(cudaMemcpy(st, h->stats, sizeof(st), cudaMemcpyDeviceToHost));
         out->sum_reward = st[0]; out->n_episodes = st[1]; out->sum_episode_length = st[2]; out->sum_episode_return = st[3];
         out->n_terminated = st[4]; out->n_truncated = st[5]; out->n_bad_state = st[6]; out->env_steps = st[7];
+        out->n_contact_overflow = st[8]; out->sum_contacts = st[9]; out->sum_solver_iterations = st[10]; out->sum_self_contacts = st[11];
     }
     return GO1_OK;
 }
@@ -1064,7 +1084,7 @@ int go1_get_contacts(go1_handle h, int env, Go1Contact* buf, int cap, int* n) {
     const int nk = (int)tmp[0];
     for (int c = 0; c < nk && c < CW && cnt < cap; c++, cnt++) {
         const real* e = tmp.data() + 1 + c * DC_STRIDE;
-        buf[cnt].geom = (int)e[0]; buf[cnt].dim = (int)e[1]; buf[cnt].dist = e[2];
+        buf[cnt].geom = (int)e[0] & 63; buf[cnt].geom1 = (int)e[0] >> 6; buf[cnt].pad_ = 0; buf[cnt].dim = (int)e[1]; buf[cnt].dist = e[2];
         for (int a = 0; a < 3; a++) buf[cnt].pos[a] = e[3 + a];
         for (int a = 0; a < 6; a++) buf[cnt].force[a] = e[6 + a];
     }

@@ -14,7 +14,7 @@ import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 
-OBS_DIM, ACT_DIM, NQ, NV, NBODY, INFO_DIM, MAX_CONTACTS = 48, 12, 19, 18, 14, 16, 64
+OBS_DIM, ACT_DIM, NQ, NV, NBODY, INFO_DIM, MAX_CONTACTS = 48, 12, 19, 18, 14, 16, 40
 BIPED_INFO_DIM = 12
 
 ACTION_RANDOM, ACTION_POLICY, ACTION_ZERO = 0, 1, 2
@@ -58,12 +58,13 @@ class Diag(C.Structure):
 
 class Contact(C.Structure):
     _fields_ = [("geom", C.c_int32), ("dim", C.c_int32), ("dist", C.c_double), ("pos", C.c_double * 3),
-                ("force", C.c_double * 6)]
+                ("force", C.c_double * 6), ("geom1", C.c_int32), ("pad_", C.c_int32)]
 
 
 class Stats(C.Structure):
     _fields_ = [(k, C.c_double) for k in ("sum_reward", "n_episodes", "sum_episode_length", "sum_episode_return",
-                                          "n_terminated", "n_truncated", "n_bad_state", "env_steps")]
+                                          "n_terminated", "n_truncated", "n_bad_state", "env_steps",
+                                          "n_contact_overflow", "sum_contacts", "sum_solver_iterations", "sum_self_contacts")]
 
 
 class Policy(C.Structure):
@@ -286,7 +287,7 @@ class Sim:
         buf = (Contact * MAX_CONTACTS)()
         n = C.c_int()
         self._check(self.lib.L.go1_get_contacts(self._h, int(env), buf, MAX_CONTACTS, C.byref(n)), "go1_get_contacts")
-        return [dict(geom=b.geom, dim=b.dim, dist=b.dist, pos=np.array(b.pos[:]), force=np.array(b.force[:]))
+        return [dict(geom=b.geom, geom1=b.geom1, dim=b.dim, dist=b.dist, pos=np.array(b.pos[:]), force=np.array(b.force[:]))
                 for b in buf[: n.value]]
 
     def set_attr(self, name: str, value: float):

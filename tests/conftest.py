@@ -38,7 +38,7 @@ CSRC = os.path.join(ROOT, "quadruped_rl_locomotion_b200", "csrc")
 def build_emu(prec: str) -> str:
     """g++ build of the CUDA source against tests/emu/cuda_emu.h (CPU SIMT emulation; test-only)."""
     out = os.path.join(EMU_DIR, f"libgo1sim_emu_{prec}.so")
-    deps = [os.path.join(CSRC, f) for f in ("go1sim.cu", "go1_warp.cuh", "go1_model.h")] + \
+    deps = [os.path.join(CSRC, f) for f in ("go1sim.cu", "go1_warp.cuh", "go1_pair.cuh", "go1_model.h")] + \
            [os.path.join(EMU_DIR, "cuda_emu.h"), os.path.join(ROOT, "include", "go1sim.h")]
     if not os.path.exists(out) or any(os.path.getmtime(d) > os.path.getmtime(out) for d in deps):
         subprocess.check_call(["g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-DGO1_EMU", "-DGO1_WARPS=1",

@@ -27,8 +27,8 @@ def load_trace(ctrl: str):
                                   "ep_last_contacts", "ep_desired_velocity", "ep_time_unhealthy", "ep_last_dev")}
     post = {k: tr[k][1:n + 1] for k in ("qpos", "qvel", "warm", "ep_feet_air_time", "ep_last_contacts",
                                         "ep_time_unhealthy", "ep_last_dev")}
-    for k in ("action", "qacc", "qfrc_actuator", "cfrc_ext", "trunk_z", "ncon", "con_geom", "con_dist", "con_fn", "obs",
-              "reward", "info", "healthy", "terminated", "truncated", "solver_iter"):
+    for k in ("action", "qacc", "qfrc_actuator", "cfrc_ext", "trunk_z", "ncon", "con_geom", "con_geom1", "con_dim", "con_dist", "con_fn",
+              "con_force", "con_pos", "obs", "reward", "info", "healthy", "terminated", "truncated", "solver_iter"):
         post[k] = tr[k][:n]
     return pre, post
 
@@ -154,11 +154,65 @@ def compare_biped(out, post, idx):
 
 
 def contact_sets_equal(contacts, post, t, tie_eps=1e-6, margin=0.001):
-    """Contact-set equality (robot geom ids with multiplicity) excluding contacts within tie_eps of the margin."""
-    gold = [(int(g), float(dd)) for g, dd in zip(post["con_geom"][t], post["con_dist"][t]) if g >= 0]
-    ours = [(c["geom"], c["dist"]) for c in contacts]
+    """Contact-set equality ((geom1, geom2) pairs with multiplicity; geom1 = 0 is the floor) excluding contacts within
+    tie_eps of the margin."""
+    gold = [(int(g1), int(g), float(dd)) for g1, g, dd in zip(post["con_geom1"][t], post["con_geom"][t], post["con_dist"][t]) if g >= 0]
+    ours = [(c["geom1"], c["geom"], c["dist"]) for c in contacts]
     near = lambda dd: abs(dd - margin) < tie_eps
-    a = sorted(g for g, dd in gold if not near(dd))
-    b = sorted(g for g, dd in ours if not near(dd))
-    excluded = sum(near(dd) for _, dd in gold) + sum(near(dd) for _, dd in ours)
+    a = sorted((g1, g) for g1, g, dd in gold if not near(dd))
+    b = sorted((g1, g) for g1, g, dd in ours if not near(dd))
+    excluded = sum(near(dd) for _, _, dd in gold) + sum(near(dd) for _, _, dd in ours)
     return a == b, excluded
+
+
+def _force_invariants(f):
+    """normal, |tangential|, torsional, |rolling| of a contact-frame force: independent of the choice of the two tangent axes
+    (MuJoCo aligns the first tangent of a plane-capsule contact with the capsule axis, the kernel keeps the floor's constant
+    frame; the cone is isotropic in the tangent plane, so the physics are the same)."""
+    f = np.asarray(f, dtype=np.float64)
+    return np.array([f[0], np.hypot(f[1], f[2]), f[3], np.hypot(f[4], f[5])])
+
+
+def compare_contacts(contacts, post, t):
+    """Per-contact comparison with the golden mjContact / efc_force records of step t (same MuJoCo order on both sides:
+    floor contacts in geom order, then robot-robot contacts in body-pair order).  Returns the worst errors of
+    dist (absolute), pos (absolute) and of the contact force RELATIVE TO THE LARGEST FORCE ROW OF THE STEP (north_star:
+    "contact forces match mj_step within 1e-5 relative"): `force` = frame-independent invariants of every contact,
+    `force_rows` = all rows of the robot-robot contacts (same frame on both sides).  None when the sets differ."""
+    n = int(post["ncon"][t])
+    if n != len(contacts) or n > post["con_geom"].shape[1]:
+        return None
+    fscale = max(1.0, float(np.abs(post["con_force"][t][:n]).max())) if n else 1.0
+    w = dict(dist=0.0, pos=0.0, force=0.0, force_rows=0.0)
+    for i, c in enumerate(contacts):
+        if c["geom"] != int(post["con_geom"][t][i]) or c["geom1"] != int(post["con_geom1"][t][i]) or c["dim"] != int(post["con_dim"][t][i]):
+            return None
+        w["dist"] = max(w["dist"], abs(c["dist"] - float(post["con_dist"][t][i])))
+        w["pos"] = max(w["pos"], float(np.abs(c["pos"] - post["con_pos"][t][i]).max()))
+        w["force"] = max(w["force"], float(np.abs(_force_invariants(c["force"]) - _force_invariants(post["con_force"][t][i])).max()) / fscale)
+        if c["geom1"] > 0:
+            w["force_rows"] = max(w["force_rows"], float(np.abs(c["force"] - post["con_force"][t][i]).max()) / fscale)
+    return w
+
+
+def self_contact_categories(post, geom_bodyid):
+    """Golden step indices by the kind of robot-robot contact they hold: cross (two different legs: dense leg block),
+    same (one leg: inside its 3x3 block), trunk (trunk vs leg), foot (condim-6 foot contact with a robot geom)."""
+    gb = np.asarray(geom_bodyid)
+    cats = dict(cross=[], same=[], trunk=[], foot=[], none=[])
+    for t in range(len(post["con_geom1"])):
+        sel = post["con_geom1"][t] > 0
+        if not sel.any():
+            cats["none"].append(t)
+            continue
+        b1 = gb[post["con_geom1"][t][sel]]; b2 = gb[post["con_geom"][t][sel]]
+        l1 = np.where(b1 >= 2, (b1 - 2) // 3, -1); l2 = np.where(b2 >= 2, (b2 - 2) // 3, -1)
+        if ((l1 >= 0) & (l2 >= 0) & (l1 != l2)).any():
+            cats["cross"].append(t)
+        if ((l1 >= 0) & (l1 == l2)).any():
+            cats["same"].append(t)
+        if ((l1 < 0) | (l2 < 0)).any():
+            cats["trunk"].append(t)
+        if (post["con_dim"][t][sel] == 6).any():
+            cats["foot"].append(t)
+    return {k: np.array(v, dtype=int) for k, v in cats.items()}

@@ -164,7 +164,8 @@ def _run_env_logic(lib, ctrl, biped, n, seed, tol):
         # time_unhealthy accumulates 0.02 s per step in the reference; k * 0.02 differs from the running sum only in the last bits,
         # so the 750 -> 751 transition is decided on the step COUNT (tests/test_env_logic.py::test_termination_needs_751_unhealthy_steps)
         o_obs, o_rew, o_term, o_trunc, o_info = logic.step(ep, act[e].astype(np.float64), d.qpos.copy(), d.qvel.copy(), d.qacc.copy(),
-                                                           d.qfrc_actuator.copy(), d.cfrc_ext.copy(), d.xpos[1, 2], kin=kin)
+                                                           d.qfrc_actuator.copy(), d.cfrc_ext.copy(), d.xpos[1, 2], kin=kin,
+                                                           n_self_collisions=el.count_self_collisions(d.contact, model.geom_bodyid) if biped else 0)
         o_term = (p["unhealthy"] + 1 > 750) if not o_info["healthy"] else False
         feet = np.linalg.norm(d.cfrc_ext[[4, 7, 10, 13]], axis=1)
         if np.any(np.abs(feet - 1.0) < 1e-3) or abs(np.linalg.norm(d.cfrc_ext[[2, 3, 5, 6, 8, 9, 11, 12]]) - 0.1) < 1e-3:

@@ -133,7 +133,8 @@ def test_live_reference_env_biped_equals_restatement(seed):
         obs, rew, term, trunc, info = env.step(a)
         d = env.data
         o2, r2, t2, tr2, i2 = logic.step(ep, a, d.qpos.copy(), d.qvel.copy(), d.qacc.copy(), d.qfrc_actuator.copy(),
-                                         d.cfrc_ext.copy(), d.xpos[1, 2], kin=biped_kin(d), prev_front_feet_forces=prev_ff)
+                                         d.cfrc_ext.copy(), d.xpos[1, 2], kin=biped_kin(d), prev_front_feet_forces=prev_ff,
+                                         n_self_collisions=el.count_self_collisions(d.contact, env.model.geom_bodyid))
         prev_ff = np.linalg.norm(d.cfrc_ext[[4, 7]], axis=1)
         assert np.allclose(obs, o2, atol=1e-12) and rew == pytest.approx(r2, rel=1e-9, abs=1e-9)
         assert (term, trunc) == (t2, tr2)

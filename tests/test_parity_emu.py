@@ -9,6 +9,7 @@ import parity_common as pc
 # tolerances (relative to the vector scale, see parity_common.rel_err); one control step = 10 mj_steps
 F64 = dict(qpos=1e-10, qvel=1e-10, qacc=1e-9, qfrc_actuator=1e-10, cfrc_ext=1e-9, trunk_z=1e-12)
 F32 = dict(qpos=2e-6, qvel=1e-5, qacc=5e-5, qfrc_actuator=1e-5, cfrc_ext=5e-3, trunk_z=1e-6, obs=1e-5, reward=1e-3, info=1e-5)
+F32_FORCE = 5e-3     # contact-frame force rows relative to the largest row of the step (see DESIGN.md, fp32 floors)
 
 
 def _sample(n_total, k, seed=0):
@@ -154,3 +155,57 @@ def test_contact_overflow_is_counted(emu_lib_f64):
     for e in range(len(over[:2])):
         assert out["diag"][e]["contact_overflow"] > 0 and out["diag"][e]["ncon"] == pc.MAX_CONTACTS_PER_ENV
         assert np.isfinite(out["state"][e]["qpos"]).all()
+
+
+def _self_contact_indices(ctrl, post, per_cat=6, seed=5):
+    from quadruped_rl_locomotion_b200.mjcf import Model
+    cats = pc.self_contact_categories(post, Model.from_blob(pc.model_blob(ctrl)).geom_bodyid)
+    rng = np.random.default_rng(seed)
+    pick = [rng.choice(v, size=min(per_cat, len(v)), replace=False) for k, v in cats.items() if k != "none" and len(v)]
+    return cats, np.unique(np.concatenate(pick)).astype(int)
+
+
+@pytest.mark.parametrize("prec", ["f64", "f32"])
+def test_robot_robot_contacts(emu_lib_f64, emu_lib_f32, prec):
+    """Rows a6/a7: steps whose golden contact list holds robot-robot contacts of every kind -- two different legs (the dense
+    12 x 12 leg block of the Hessian), one leg (foot against its own hip motor), trunk vs leg, condim-6 foot contacts.
+    State, contact set INCLUDING geom1, per-contact dist / pos / force rows against the oracle's mjContact + efc_force."""
+    lib = emu_lib_f64 if prec == "f64" else emu_lib_f32
+    pre, post = pc.load_starts("torque")
+    cats, idx = _self_contact_indices("torque", post)
+    assert all(len(cats[k]) > 0 for k in ("cross", "same", "foot")), {k: len(v) for k, v in cats.items()}
+    pre_t, post_t = pc.load_trace("torque")
+    cats_t, idx_t = _self_contact_indices("torque", post_t)
+    assert len(cats_t["trunk"]) > 0
+    for (p0, p1, ii) in ((pre, post, idx), (pre_t, post_t, np.unique(np.concatenate([idx_t, cats_t["trunk"]])))):
+        out = pc.run_teacher_forced(lib, "torque", p0, p1, ii, capture_contacts=True)
+        w, mism = pc.compare(out, p0, p1, ii)
+        tol = F64 if prec == "f64" else F32
+        for k, v in tol.items():
+            assert w[k] <= v, (k, w[k])
+        assert all(v == 0 for v in mism.values()), mism
+        worst = dict(dist=0.0, pos=0.0, force=0.0, force_rows=0.0)
+        for e, t in enumerate(ii):
+            assert out["diag"][e]["contact_overflow"] == 0
+            ok, _ = pc.contact_sets_equal(out["contacts"][e], p1, t)
+            assert ok, f"contact set differs at golden index {t}"
+            cw = pc.compare_contacts(out["contacts"][e], p1, t)
+            if cw is not None:
+                for k in worst:
+                    worst[k] = max(worst[k], cw[k])
+        lim = dict(dist=1e-12, pos=1e-11, force=1e-8, force_rows=1e-8) if prec == "f64" else dict(dist=2e-7, pos=2e-6, force=F32_FORCE, force_rows=F32_FORCE)
+        for k in worst:
+            assert worst[k] <= lim[k], (k, worst)
+
+
+def test_biped_self_collision_cost(emu_lib_f64):
+    """go1_mujoco_env.py:269-312: 25 x the number of contacts between the front-right and front-left limbs (or the rear pair)."""
+    pre, post = pc.load_starts("torque", biped=True)
+    hit = np.flatnonzero(post["binfo"][:, 9] != 0)
+    assert len(hit) >= 1
+    idx = np.unique(np.concatenate([hit, hit - 1, [0, 1]])).astype(int)
+    out = pc.run_teacher_forced(emu_lib_f64, "torque", pre, post, idx, biped=True)
+    worst, flags = pc.compare_biped(out, post, idx)
+    assert worst.max() <= 1e-6, worst
+    for e, t in enumerate(idx):
+        assert abs(out["binfo"][e, 9] - post["binfo"][t, 9]) < 1e-6

@@ -7,7 +7,9 @@ A "step" is one control step (frame_skip=10 mj_steps + obs/reward/termination/au
 environment of the slab: 16384 envs per GPU, torque control, random actions U[-1,1] generated on the
 device (BASELINE config 3(i)); `value` = env-steps/s summed over ranks with state resident in HBM;
 `e2e` = the same through Go1CudaVecEnv.step (host numpy actions in, host obs/reward/done out).
-One process per GPU (torchrun), no data-path collective: only the max-over-ranks timing is reduced.
+One process per GPU (torchrun), no data-path collective: the max-over-ranks timing and, every 100 control steps, the
+12 rollout statistics (BASELINE config 4) are all-reduced over NCCL.  The timed window is STEADY STATE whatever --warmup
+says: an untimed burn-in (burn_in) brings the slab to the stationary mix of episode phases first.
 """
 from __future__ import annotations
 
@@ -34,9 +36,42 @@ ALG_FLOP_PER_ENV_STEP = 0.67e6     # SURVEY 8(d) nominal (10 substeps x (25k + 3
 # instead of the nominal 3 and the redundancy of lane-parallel evaluation make up the difference to the nominal figure
 NCU_EXECUTED_FLOP_PER_ENV_STEP = 1.15e6
 FP32_FMA_MEASURED_TFLOPS = 72.1    # tools/ubench/fma.cu on this pool's B200 (148 SMs, 1965 MHz): 97 % of 148 x 128 x 2 x 1.965 GHz
-# dram__bytes_read.sum + dram__bytes_write.sum of ONE k_step launch at 16384 envs, from the committed ncu --set full capture
-# (profiles/r1_ncu_k_step_final_raw_selected.txt): 9.96 MB + 18.08 MB
-NCU_DRAM_BYTES_PER_LAUNCH_16K = 28.05e6
+BURNIN_FALL, BURNIN_MIX = 300, 100   # untimed control steps before / after the episode phases are staggered (see burn_in)
+STATS_EVERY = 100                    # BASELINE config 4: the rollout statistics are all-reduced every 100 control steps
+
+
+def kernel_source_sha():
+    """sha256 over the kernel sources: ties an ncu capture (profiles/*traffic*.json) to the code it was taken from."""
+    import hashlib
+    h = hashlib.sha256()
+    d = os.path.join(ROOT, "quadruped_rl_locomotion_b200", "csrc")
+    for f in sorted(os.listdir(d)):
+        if f.endswith((".cu", ".cuh", ".h")):
+            h.update(open(os.path.join(d, f), "rb").read())
+    return h.hexdigest()[:16]
+
+
+def ncu_traffic(n_envs, ctrl):
+    """dram__bytes_read.sum + dram__bytes_write.sum of ONE k_step launch from the committed `ncu --set full` capture of THIS
+    kernel source (profiles/r2_ncu_k_step_traffic.json, written by tools/ncu_traffic.py); None when the capture is stale."""
+    p = os.path.join(ROOT, "profiles", "r2_ncu_k_step_traffic.json")
+    try:
+        t = json.load(open(p))
+        if t.get("kernel_source_sha") == kernel_source_sha() and t.get("n_envs") == n_envs and t.get("ctrl") == ctrl:
+            return float(t["dram_bytes_per_launch"])
+    except Exception:  # noqa: BLE001
+        pass
+    return None
+
+
+def burn_in(sim, mode, policy):
+    """Brings a freshly reset slab to the stationary mix of episode phases WITHOUT timing it: the robots fall under random torques
+    (BURNIN_FALL steps), the consecutive-unhealthy counters are spread over [0, 750] (go1_stagger_phases), BURNIN_MIX more steps.
+    From then on ~N/750 episodes end per control step, so every timed window holds terminations, auto-resets, fresh upright
+    starts and long-fallen many-contact states in their steady-state proportions."""
+    sim.rollout(BURNIN_FALL, mode, policy)
+    sim.stagger_phases()
+    sim.rollout(BURNIN_MIX, mode, policy)
 
 
 def _peaks():
@@ -193,6 +228,7 @@ def run_ours(args, rank, world, local):
             dist.barrier()
         torch.cuda.synchronize()
 
+    burn_in(sim, mode, policy)
     for _ in range(args.warmup):
         sim.rollout(1, mode, policy)
     barrier()
@@ -200,12 +236,29 @@ def run_ours(args, rank, world, local):
     t0 = time.time()
     dev_ms, launches = 0.0, 0
     stats = None
-    for _ in range(args.steps):
+    STAT_KEYS = ("sum_reward", "n_episodes", "sum_episode_length", "sum_episode_return", "n_terminated", "n_truncated", "n_bad_state",
+                 "env_steps", "n_contact_overflow", "sum_contacts", "sum_solver_iterations", "sum_self_contacts")
+    gstats = torch.zeros(len(STAT_KEYS), dtype=torch.float64, device="cuda")     # global (all ranks) statistics
+    pending = torch.zeros_like(gstats)
+    n_allreduce = 0
+
+    def reduce_stats():
+        nonlocal n_allreduce
+        if world > 1:
+            dist.all_reduce(pending, op=dist.ReduceOp.SUM)     # NCCL over NVLink: 12 doubles (config 4)
+        gstats.add_(pending); pending.zero_()
+        n_allreduce += 1
+
+    for it in range(args.steps):
         flush.zero_()                      # L2 flush between timed iterations (not timed)
         torch.cuda.synchronize()
         st = sim.rollout(1, mode, policy)  # CUDA events on the launch stream inside go1_rollout
         dev_ms += st["device_ms"]; launches += st["launches"]
         stats = st if stats is None else {k: stats[k] + st[k] for k in st}
+        pending += torch.tensor([st[k] for k in STAT_KEYS], dtype=torch.float64, device="cuda")
+        if (it + 1) % STATS_EVERY == 0:
+            reduce_stats()
+    reduce_stats()
     barrier()
     t1 = time.time()
     clk = clocks.stop(t0, t1)
@@ -214,11 +267,15 @@ def run_ours(args, rank, world, local):
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
     ms_max = float(ms.item())
     value = world * n * args.steps / (ms_max * 1e-3)
+    g = dict(zip(STAT_KEYS, gstats.tolist()))
+    if args.steps >= 200:
+        assert g["n_episodes"] > 0, "a steady-state window of >= 200 control steps must contain episode ends"
 
     # ---- e2e through the public API: host actions -> VecEnv.step -> host obs/reward/done
     sim.close()
     env = Go1CudaVecEnv(n, ctrl_type=args.ctrl, biped=bool(args.biped), device=local, seed=1234, env_id_offset=rank * n, library=lib)
     env.reset()
+    burn_in(env.sim, ACTION_RANDOM, None)       # same stationary mix as the device-timed run (untimed)
     lo, hi = env.action_space.low, env.action_space.high
     rng = np.random.default_rng(rank)
     acts = [rng.uniform(lo, hi, size=(n, 12)).astype(np.float32) for _ in range(4)]
@@ -253,9 +310,10 @@ def run_ours(args, rank, world, local):
             "data": "synthetic",
             "config": {"workload": f"Go1 {args.ctrl} control{' (biped mode)' if args.biped else ''}, {n} envs/GPU, {args.actions} actions, frame_skip 10, fused obs/reward/auto-reset",
                        "envs_per_gpu": n, "parallelism": f"env-slab x{world} (no data-path collective)",
-                       "l2": "flushed between timed steps (256 MiB write, untimed)", "timing": "CUDA events on the launch stream, max over ranks"},
+                       "l2": "flushed between timed steps (256 MiB write, untimed)", "timing": "CUDA events on the launch stream, max over ranks",
+                       "state": "steady state (staggered episode phases, see steady_state)", "physics": "floor + robot-robot contacts"},
             "roofline": {"bound": "hbm", "achieved": ach_gbs, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": ach_gbs / peaks["hbm_gbs"],
-                         "traffic": NCU_DRAM_BYTES_PER_LAUNCH_16K if (n == ENVS_PER_GPU and args.ctrl == "torque") else None,
+                         "traffic": ncu_traffic(n, args.ctrl), "traffic_source": "profiles/r2_ncu_k_step_traffic.json (ncu --set full of this kernel source; null = no capture of this source)",
                          "algorithmic_bytes_per_launch": ALG_BYTES_PER_ENV_STEP * n, "peak_source": pk,
                          "note": "neither HBM nor FP32 binds: the GPC instruction cache does (gcc instruction requests at 80 % of "
                                  "peak, DESIGN.md section 3); see fp32 block",
@@ -270,7 +328,14 @@ def run_ours(args, rank, world, local):
                     "d2h_bytes_per_step": n * (48 * 4 + 4 + 1 + 1 + 48 * 4 + 16 * 4), "steps": e2e_steps,
                     "api": "Go1CudaVecEnv.step(np.ndarray[N,12]) -> (obs[N,48] f64, rew, dones, infos)"},
             "gpu_launches": launches, "clocks": clk,
-            "rollout_stats": {k: stats[k] for k in ("sum_reward", "n_episodes", "n_terminated", "n_truncated", "n_bad_state", "env_steps")},
+            "rollout_stats": dict(g, scope=f"all {world} ranks, NCCL all-reduce every {STATS_EVERY} control steps ({n_allreduce} all-reduces)"),
+            "steady_state": {"burn_in": f"{BURNIN_FALL} untimed control steps, go1_stagger_phases, {BURNIN_MIX} more (+ --warmup)",
+                             "episodes_per_step": g["n_episodes"] / max(1, args.steps),
+                             "newton_iterations_per_env_step": g["sum_solver_iterations"] / max(1.0, g["env_steps"]),
+                             "contacts_per_env": g["sum_contacts"] / max(1.0, g["env_steps"]),
+                             "robot_robot_contacts_per_env": g["sum_self_contacts"] / max(1.0, g["env_steps"]),
+                             "contacts_dropped": g["n_contact_overflow"]},
+            "kernel_source_sha": kernel_source_sha(),
         }
         emit(line)
     if world > 1:

@@ -45,7 +45,7 @@ extern "C" {
 #define GO1_INFO_DIM 16
 #define GO1_BIPED_INFO_DIM 12
 #define GO1_MAX_CONTACTS 40        /* contacts kept per environment and substep (floor + robot-robot); more are dropped and counted */
-#define GO1_MAX_PAIR_CONTACTS 8    /* robot-robot contacts among them */
+#define GO1_MAX_PAIR_CONTACTS 16   /* robot-robot contacts among them */
 
 enum {
     GO1_OK = 0,
@@ -195,6 +195,11 @@ int go1_host_unregister(go1_handle h, void* ptr);
 /* device-resident stepping loop (throughput path): n_steps control steps with actions produced on the
  * device; accumulates stats on the device and copies them to *out (nullable) at the end (synchronous). */
 int go1_rollout(go1_handle h, int n_steps, int action_mode, const Go1Policy* policy, Go1Stats* out, void* stream);
+/* Throughput runs only (no counterpart in the reference: SubprocVecEnv workers de-synchronise by themselves, test_max_envs.py:129-138):
+ * a slab that was reset all at once terminates all at once ~800 control steps later.  Sets the consecutive-unhealthy-step counter
+ * (go1_mujoco_env.py:487-493) of every currently unhealthy environment to a Philox draw in [0, max_unhealthy_steps], so that episode ends
+ * (and the auto-reset path) arrive at a uniform rate.  Physics state untouched. */
+int go1_stagger_phases(go1_handle h);
 /* elapsed device time (ms, CUDA events on the launch stream) and kernel launches of the last go1_rollout */
 int go1_last_rollout_timing(go1_handle h, float* ms, int* launches);
 

@@ -750,33 +750,50 @@ static int sphereCylinderRaw(const double *c, double r, const double *p2, const 
     memcpy(con->frame, n, 24);
     return 1;
 }
-/* d/dt of half the squared distance between the capsule-axis point pc + t*av (t in [-1, 1]) and a box /
- * cylinder given in ITS frame (pl = pc, al = av in that frame; cylinder: box == 0, sz = {R, R, h}) */
-static double seg_grad(const double *pl, const double *al, const double *sz, int box, double t) {
+/* g(t) = d/dt of half the squared distance between the capsule-axis point pl + t*al (t in [-1, 1]) and a box / solid cylinder
+ * given in ITS frame (cylinder: box == 0, sz = {R, R, h}), and g'(t).  g is continuous and non-decreasing. */
+static void seg_grad(const double *pl, const double *al, const double *sz, int box, double t, double *g, double *dg) {
     double x[3] = {pl[0] + t * al[0], pl[1] + t * al[1], pl[2] + t * al[2]};
+    *g = 0; *dg = 0;
     if (box) {
-        double g = 0;
-        for (int i = 0; i < 3; i++) { double ex = x[i] - fmin(sz[i], fmax(-sz[i], x[i])); g += ex * al[i]; }
-        return g;
+        for (int i = 0; i < 3; i++) {
+            double ex = x[i] - fmin(sz[i], fmax(-sz[i], x[i]));
+            *g += ex * al[i];
+            if (ex != 0) *dg += al[i] * al[i];
+        }
+        return;
     }
+    double ez = x[2] - fmin(sz[2], fmax(-sz[2], x[2]));
+    *g = ez * al[2];
+    if (ez != 0) *dg = al[2] * al[2];
     double rho = sqrt(x[0] * x[0] + x[1] * x[1]);
-    double ez = x[2] - fmin(sz[2], fmax(-sz[2], x[2])), g = ez * al[2];
-    if (rho > sz[0]) g += (rho - sz[0]) * (x[0] * al[0] + x[1] * al[1]) / rho;
-    return g;
-}
-#define SEG_BISECT 40
-/* parameter of the capsule-axis point closest to the box / cylinder (convex 1-D problem: bisection on the sign of the
- * derivative, fixed trip count so that the kernel and the oracle take the same path) */
-static double seg_closest(const double *pl, const double *al, const double *sz, int box) {
-    double glo = seg_grad(pl, al, sz, box, -1.0), ghi = seg_grad(pl, al, sz, box, 1.0);
-    if (glo >= 0) return -1.0;
-    if (ghi <= 0) return 1.0;
-    double lo = -1.0, hi = 1.0;
-    for (int it = 0; it < SEG_BISECT; it++) {
-        double mid = 0.5 * (lo + hi);
-        if (seg_grad(pl, al, sz, box, mid) < 0) lo = mid; else hi = mid;
+    if (rho > sz[0]) {
+        double u = (x[0] * al[0] + x[1] * al[1]) / rho, a2 = al[0] * al[0] + al[1] * al[1];
+        *g += (rho - sz[0]) * u;
+        *dg += u * u + (rho - sz[0]) * (a2 - u * u) / rho;
     }
-    return 0.5 * (lo + hi);
+}
+/* parameter of the capsule-axis point closest to the box / cylinder: root of the monotone g by Newton steps kept inside a
+ * shrinking bracket (bisection when the step leaves it); the kernel runs the identical iteration (go1_pair.cuh) */
+static double seg_closest(const double *pl, const double *al, const double *sz, int box) {
+    double glo, ghi, dg;
+    seg_grad(pl, al, sz, box, -1.0, &glo, &dg);
+    if (glo >= 0) return -1.0;
+    seg_grad(pl, al, sz, box, 1.0, &ghi, &dg);
+    if (ghi <= 0) return 1.0;
+    double lo = -1.0, hi = 1.0, t = lo - glo * (hi - lo) / (ghi - glo);
+    for (int it = 0; it < 24; it++) {
+        double gt;
+        seg_grad(pl, al, sz, box, t, &gt, &dg);
+        if (gt == 0) break;
+        if (gt < 0) lo = t; else hi = t;
+        double tn = dg > 0 ? t - gt / dg : 0.5 * (lo + hi);
+        if (!(tn > lo && tn < hi)) tn = 0.5 * (lo + hi);
+        int done = fabs(tn - t) <= 1e-13;
+        t = tn;
+        if (done) break;
+    }
+    return t;
 }
 /* capsule (geom1) vs box or cylinder (geom2) */
 static int capsuleConvex(const double *p1, const double *m1, const double *s1, const double *p2, const double *m2, const double *s2,

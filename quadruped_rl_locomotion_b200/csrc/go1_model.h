@@ -19,7 +19,7 @@ constexpr int GMAX = 12;      // collision geoms handled by one lane (its leg's 
 constexpr int CMAX = 16;      // active contacts kept per lane
 constexpr int NCLS = 8;       // distinct contact parameter classes (floor-mixed + robot-robot mixed)
 constexpr int NKIND = 4;      // distinct per-geom contact parameter sets
-constexpr int NBP = 72;       // body pairs that may collide (not parent and child, not hip-hip)
+constexpr int NGP = 704;      // candidate geom pairs of the robot-robot collision (bodies not parent and child, no cylinder-cylinder)
 constexpr int GFLAT = 44;     // robot collision geoms (flat list, sorted by body)
 
 // index tables of the block-arrow layout tt[21] | tk[4][6][3] | kk[4][6]  (go1_warp.cuh)
@@ -69,16 +69,14 @@ struct DevModel {
     DevGeom<T> flat[GFLAT];
     T flat_rb[GFLAT];
     ArrowTab tab;
-    // robot-robot collision (mj_collision body pairs; go1_pair.cuh): flat-geom range and bounding sphere per body, body pairs in
-    // (body1, body2) order, class of a contact between geoms of kinds (a, b)
-    int body_g0[16];
-    T bsph[13][4];
-    int npairs, pair_margin_pad;
-    unsigned char pair_a[NBP], pair_b[NBP];
+    // robot-robot collision (go1_pair.cuh): number of candidate geom pairs, class of a contact between geoms of kinds (a, b)
+    int ngp, pad2;
     int pair_cls[NKIND][NKIND];
     T pair_margin;
     // env constants
     T key_qpos[19], key_ctrl[12], soft_lo[12], soft_hi[12], ctrl_lo[12], ctrl_hi[12];
+    // ---- NOT staged in shared memory (read through EnvCfg::gp_tab): candidate geom pairs (flat indices) in mj_collision's order
+    unsigned char gp_a[NGP], gp_b[NGP];
 };
 
 // ---------------------------------------------------------------------------------------------
@@ -413,37 +411,29 @@ inline bool build_dev_model(const void* data, size_t nbytes, DevModel<double>& M
     }
     // ---- robot-robot collision tables (mj_collision: body pairs that are not parent and child; geoms of one body never collide)
     {
+        int body_g0[15];
         for (int b = 0; b <= 13; b++) {
             int g = 0;
             while (g < M.nflat && M.flat[g].slot < b) g++;
-            M.body_g0[b] = g;
+            body_g0[b] = g;
         }
-        M.body_g0[14] = M.body_g0[15] = M.nflat;
-        for (int b = 0; b < 13; b++) {
-            const int g0 = M.body_g0[b], g1 = M.body_g0[b + 1];
-            double c[3] = {0, 0, 0}, r = 0;
-            for (int g = g0; g < g1; g++) for (int k = 0; k < 3; k++) c[k] += M.flat[g].pos[k] / (g1 - g0);
-            for (int g = g0; g < g1; g++) {
-                double d2 = 0;
-                for (int k = 0; k < 3; k++) d2 += (M.flat[g].pos[k] - c[k]) * (M.flat[g].pos[k] - c[k]);
-                r = std::fmax(r, std::sqrt(d2) + M.flat_rb[g]);
-            }
-            for (int k = 0; k < 3; k++) M.bsph[b][k] = c[k];
-            M.bsph[b][3] = g1 > g0 ? r * (1 + 1e-6) : -1.0;
-        }
+        body_g0[14] = M.nflat;
         auto parent = [](int b) { return b == 0 ? -1 : ((b - 1) % 3 == 0 ? 0 : b - 1); };
-        auto only_cyl = [&](int b) { for (int g = M.body_g0[b]; g < M.body_g0[b + 1]; g++) if (M.flat[g].type != G_CYLINDER) return false; return true; };
-        M.npairs = 0;
+        M.ngp = 0;
         M.pair_margin = 0;
         for (int a = 0; a < 13; a++)
             for (int b = a + 1; b < 13; b++) {
                 if (parent(b) == a || parent(a) == b) continue;
-                if (M.body_g0[a + 1] == M.body_g0[a] || M.body_g0[b + 1] == M.body_g0[b]) continue;
-                // cylinder-cylinder (hip motor vs hip motor; MuJoCo: MPR) is not collided: DESIGN.md states the reach of that pair
-                if (only_cyl(a) && only_cyl(b)) continue;
-                GO1_REQ((M.body_g0[a + 1] - M.body_g0[a]) * (M.body_g0[b + 1] - M.body_g0[b]) <= 32, "more than 32 geom pairs in one body pair");
-                GO1_REQ(M.npairs < NBP, "too many colliding body pairs");
-                M.pair_a[M.npairs] = (unsigned char)a; M.pair_b[M.npairs] = (unsigned char)b; M.npairs++;
+                for (int g1 = body_g0[a]; g1 < body_g0[a + 1]; g1++)
+                    for (int g2 = body_g0[b]; g2 < body_g0[b + 1]; g2++) {
+                        // cylinder-cylinder (hip motor vs hip motor; MuJoCo: MPR) is not collided: DESIGN.md states the reach of that pair
+                        if (M.flat[g1].type == G_CYLINDER && M.flat[g2].type == G_CYLINDER) continue;
+                        const int lo = std::min(M.flat[g1].type, M.flat[g2].type), hi = std::max(M.flat[g1].type, M.flat[g2].type);
+                        GO1_REQ(lo == G_SPHERE || lo == G_CAPSULE, "robot-robot pair without a sphere or capsule is not implemented");
+                        (void)hi;
+                        GO1_REQ(M.ngp < NGP, "too many candidate geom pairs");
+                        M.gp_a[M.ngp] = (unsigned char)g1; M.gp_b[M.ngp] = (unsigned char)g2; M.ngp++;
+                    }
             }
         for (int ka = 0; ka < NKIND; ka++)
             for (int kb = 0; kb < NKIND; kb++) {
@@ -509,7 +499,7 @@ inline void cast_dev_model(const DevModel<double>& S, DevModel<T>& D) {
     CPA(act_gear); CPA(act_gain); CPA(act_b0); CPA(act_b1); CPA(act_b2); CPA(act_clo); CPA(act_chi); CPA(act_flo); CPA(act_fhi);
     D.nflat = S.nflat;
     CPA(flat_rb); CPI(tab);
-    CPI(body_g0); CPA(bsph); D.npairs = S.npairs; CPI(pair_a); CPI(pair_b); CPI(pair_cls); CP(pair_margin);
+    D.ngp = S.ngp; CPI(pair_cls); CP(pair_margin); CPI(gp_a); CPI(gp_b);
     for (int g = 0; g < GFLAT; g++) {
         const DevGeom<double>& s = S.flat[g]; DevGeom<T>& d = D.flat[g];
         d.type = s.type; d.slot = s.slot; d.cls = s.cls; d.gid = s.gid; d.kind = s.kind;

@@ -140,20 +140,57 @@ GO1_DEV void pp_sphere_cyl(const T* c, T r, const GeomW<T>& q, T margin, T inc, 
     if (cd < inc) stage2_emit(st, pos, n, cd);
 }
 
-// d/dt of half the squared distance between pl + t*al and a box (half sizes sz) / cylinder (sz = R, R, h) in its own frame
-template <typename T> GO1_DEV T seg_grad(const T* pl, const T* al, const T* sz, bool box, T t) {
+// g(t) = d/dt of half the squared distance between pl + t*al and a box (half sizes sz) / solid cylinder (sz = R, R, h) given in
+// its own frame, and g'(t).  g is continuous and non-decreasing (the squared distance to a convex set is convex along a line).
+template <typename T> GO1_DEV void seg_grad(const T* pl, const T* al, const T* sz, bool box, T t, T& g, T& dg) {
     typedef Num<T> N;
     const T x[3] = {pl[0] + t * al[0], pl[1] + t * al[1], pl[2] + t * al[2]};
+    g = 0; dg = 0;
     if (box) {
-        T g = 0;
 #pragma unroll
-        for (int i = 0; i < 3; i++) g += (x[i] - N::min_(sz[i], N::max_(-sz[i], x[i]))) * al[i];
-        return g;
+        for (int i = 0; i < 3; i++) {
+            const T ex = x[i] - N::min_(sz[i], N::max_(-sz[i], x[i]));
+            g += ex * al[i];
+            if (ex != 0) dg += al[i] * al[i];
+        }
+        return;
     }
+    const T ez = x[2] - N::min_(sz[2], N::max_(-sz[2], x[2]));
+    g = ez * al[2];
+    if (ez != 0) dg = al[2] * al[2];
     const T rho = N::sqrt_(x[0] * x[0] + x[1] * x[1]);
-    T g = (x[2] - N::min_(sz[2], N::max_(-sz[2], x[2]))) * al[2];
-    if (rho > sz[0]) g += (rho - sz[0]) * (x[0] * al[0] + x[1] * al[1]) / rho;
-    return g;
+    if (rho > sz[0]) {
+        const T u = (x[0] * al[0] + x[1] * al[1]) / rho, a2 = al[0] * al[0] + al[1] * al[1];
+        g += (rho - sz[0]) * u;
+        dg += u * u + (rho - sz[0]) * (a2 - u * u) / rho;
+    }
+}
+
+// parameter t in [-1, 1] of the capsule-axis point closest to the box / cylinder: root of the monotone g by Newton steps
+// kept inside a shrinking bracket (bisection when the step leaves it); the oracle runs the identical iteration
+template <typename T> GO1_DEV T seg_closest(const T* pl, const T* al, const T* sz, bool box) {
+    typedef Num<T> N;
+    T glo, ghi, dg;
+    seg_grad(pl, al, sz, box, T(-1), glo, dg);
+    if (glo >= 0) return T(-1);
+    seg_grad(pl, al, sz, box, T(1), ghi, dg);
+    if (ghi <= 0) return T(1);
+    T lo = -1, hi = 1;
+    T t = lo - glo * (hi - lo) / (ghi - glo);
+    const T eps = sizeof(T) == 4 ? T(1e-6) : T(1e-13);
+#pragma unroll 1
+    for (int it = 0; it < 24; it++) {
+        T gt;
+        seg_grad(pl, al, sz, box, t, gt, dg);
+        if (gt == 0) break;
+        if (gt < 0) lo = t; else hi = t;
+        T tn = dg > 0 ? t - gt / dg : T(0.5) * (lo + hi);
+        if (!(tn > lo && tn < hi)) tn = T(0.5) * (lo + hi);
+        const bool done = N::abs_(tn - t) <= eps;
+        t = tn;
+        if (done) break;
+    }
+    return t;
 }
 
 // capsule a (geom1) vs box / cylinder q (geom2)
@@ -170,19 +207,7 @@ GO1_DEV void pp_capsule_convex(const GeomW<T>& a, const GeomW<T>& q, bool box, T
         const T lim = sz[i] + a.s[0] + margin, u = pl[i] - al[i], v = pl[i] + al[i];
         if ((u > lim && v > lim) || (u < -lim && v < -lim)) return;
     }
-    T ts;
-    const T glo = seg_grad(pl, al, sz, box, T(-1)), ghi = seg_grad(pl, al, sz, box, T(1));
-    if (glo >= 0) ts = -1;
-    else if (ghi <= 0) ts = 1;
-    else {
-        T lo = -1, hi = 1;
-#pragma unroll 1
-        for (int it = 0; it < (sizeof(T) == 4 ? 26 : 40); it++) {
-            const T mid = T(0.5) * (lo + hi);
-            if (seg_grad(pl, al, sz, box, mid) < 0) lo = mid; else hi = mid;
-        }
-        ts = T(0.5) * (lo + hi);
-    }
+    const T ts = seg_closest(pl, al, sz, box);
 #pragma unroll 1
     for (int e = 0; e < 2; e++) {
         if (e == 1 && (!box || st.cnt == 0)) break;

@@ -18,6 +18,9 @@
 #pragma once
 #include "go1_model.h"
 
+#ifdef GO1_EMU_COUNT
+extern long g_emu_rounds[4];
+#endif
 namespace go1 {
 
 #define GO1_DEV __device__ __forceinline__
@@ -35,6 +38,19 @@ constexpr int NDOF = 18;    // 0..5 trunk (3 lin world, 3 rot body frame), 6 + 3
 #ifndef GO1_LS_FAST_MAX
 #define GO1_LS_FAST_MAX 10
 #endif
+#ifndef GO1_PHASE_BARRIERS
+#define GO1_PHASE_BARRIERS 1  // block barriers at the phase boundaries inside a substep / Newton round (see GO1_PB)
+#endif
+// The warps of a block run different environments; data-dependent phases (robot-robot narrowphase, pair Hessian, the
+// coupled-leg factorisation, line-search trip counts) let them drift apart inside a round, and every drifted warp is its
+// own instruction-fetch stream (the kernel is bound by instruction delivery).  A block barrier at
+// each phase boundary regroups them.  Every warp of the block executes the same NUMBER of barriers per round / substep.
+#if GO1_LOCKSTEP && GO1_PHASE_BARRIERS
+#define GO1_PB() __syncthreads()
+#else
+#define GO1_PB() ((void)0)
+#endif
+#define GO1_PB3() do { GO1_PB(); GO1_PB(); GO1_PB(); } while (0)
 #ifndef GO1_WARM_EXTRAP
 #define GO1_WARM_EXTRAP 1     // fp32 build: warm start = 2 a(t-1) - a(t-2) inside a control step (see substep_w)
 #endif
@@ -55,7 +71,7 @@ constexpr int NDOF = 18;    // 0..5 trunk (3 lin world, 3 rot body frame), 6 + 3
 #endif
 constexpr int CW = GO1_CW;  // contacts kept per environment (geom order; the rest is counted as overflow)
 #ifndef GO1_PW
-#define GO1_PW 8
+#define GO1_PW 16
 #endif
 constexpr int PW = GO1_PW;  // robot-robot contacts kept per environment (stored after the floor contacts; both share the CW slots)
 constexpr int NARROW = 117; // block-arrow storage: tt[21] | tk[4][6][3] | kk[4][6]
@@ -207,6 +223,7 @@ template <typename T> struct WEnv {
     GO1_DEV T (*wrench())[6] { return bv[1]; }
     GO1_DEV T* kd() { return &Kc[0][0]; }              // dense 12x12 leg block of the Hessian (environments with leg-leg contacts)
     GO1_DEV T* jbuf() { return &Kc[0][0] + 144; }      // 6 x 12 Jacobian rows of one robot-robot contact
+    GO1_DEV T* g6() { return &Kc[0][0] + 216; }        // packed 6x6 block of one coupled pair of legs (21) + its 3x3 coupling block (9)
 };
 
 GO1_DEV int meta_b2(int meta) { return meta & 15; }
@@ -501,6 +518,134 @@ template <typename T> GO1_NOINL T arrow_solve(WEnv<T>& E, const T* F, T g, int l
 }
 
 
+// ---- exactly one pair of legs la < lb coupled by leg-leg contacts: their 6 dofs form one dense block G6 (packed, E.g6(), built
+// by pair_hessian), the other two legs keep their 3x3 blocks.  Same elimination as arrow_factor, with a 6x6 Cholesky for the
+// pair; the rows of Y that belong to the pair go back into the tk slots of the two legs, so the Schur sum is unchanged.
+template <typename T> GO1_NOINL void pairleg_factor(WEnv<T>& E, const DevModel<T>& m, T* A, int la, int lb, int lane) {
+    typedef Num<T> N;
+    T* G = E.g6();
+    if (lane < 4 && lane != la && lane != lb) {
+        T* a = A + A_KK + 6 * lane;
+        const T i00 = N::rsqrt_(N::max_(a[0], N::MINVAL));
+        const T l10 = a[1] * i00, l20 = a[3] * i00;
+        const T i11 = N::rsqrt_(N::max_(a[2] - l10 * l10, N::MINVAL));
+        const T l21 = (a[4] - l20 * l10) * i11;
+        const T i22 = N::rsqrt_(N::max_(a[5] - l20 * l20 - l21 * l21, N::MINVAL));
+        a[0] = i00; a[1] = l10; a[2] = i11; a[3] = l20; a[4] = l21; a[5] = i22;
+    }
+    chol6(G, lane);
+    if (lane < 24) {
+        const int k = lane / 6, j = lane - 6 * k;
+        if (k != la && k != lb) {
+            const T* l = A + A_KK + 6 * k;
+            T* y = A + A_TK + 18 * k + 3 * j;
+            const T y0 = y[0] * l[0];
+            const T y1 = (y[1] - y0 * l[1]) * l[2];
+            const T y2 = (y[2] - y0 * l[3] - y1 * l[4]) * l[5];
+            y[0] = y0; y[1] = y1; y[2] = y2;
+        }
+    } else if (lane < 30) {          // trunk row lane - 24 of the pair's coupling [C_la C_lb] L6^-T
+        const int t = lane - 24;
+        T* ya = A + A_TK + 18 * la + 3 * t; T* yb = A + A_TK + 18 * lb + 3 * t;
+        T y[6] = {ya[0], ya[1], ya[2], yb[0], yb[1], yb[2]};
+#pragma unroll
+        for (int c = 0; c < 6; c++) {
+            T v = y[c];
+#pragma unroll
+            for (int p = 0; p < c; p++) v -= y[p] * G[SYM(c, p)];
+            y[c] = v * G[SYM(c, c)];
+        }
+        ya[0] = y[0]; ya[1] = y[1]; ya[2] = y[2]; yb[0] = y[3]; yb[1] = y[4]; yb[2] = y[5];
+    }
+    __syncwarp();
+    if (lane < 21) {
+        const int r = m.tab.sym_r[lane], c = m.tab.sym_c[lane];
+        T s = 0;
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            const T* yr = A + A_TK + 18 * k + 3 * r; const T* yc = A + A_TK + 18 * k + 3 * c;
+            s += yr[0] * yc[0] + yr[1] * yc[1] + yr[2] * yc[2];
+        }
+        A[lane] -= s;
+    }
+    __syncwarp();
+    chol6(A, lane);
+}
+
+template <typename T> GO1_NOINL T pairleg_solve(WEnv<T>& E, const T* F, T g, int la, int lb, int lane) {
+    const T* G = E.g6();
+    if (lane < NDOF) E.xv[lane] = g;
+    __syncwarp();
+    if (lane < 4 && lane != la && lane != lb) {
+        const T* l = F + A_KK + 6 * lane; T* z = E.xv + 6 + 3 * lane;
+        const T z0 = z[0] * l[0];
+        const T z1 = (z[1] - l[1] * z0) * l[2];
+        const T z2 = (z[2] - l[3] * z0 - l[4] * z1) * l[5];
+        z[0] = z0; z[1] = z1; z[2] = z2;
+    } else if (lane == 4) {
+        T* za = E.xv + 6 + 3 * la; T* zb = E.xv + 6 + 3 * lb;
+        T z[6] = {za[0], za[1], za[2], zb[0], zb[1], zb[2]};
+#pragma unroll
+        for (int i = 0; i < 6; i++) {
+            T s = z[i];
+#pragma unroll
+            for (int k = 0; k < i; k++) s -= G[SYM(i, k)] * z[k];
+            z[i] = s * G[SYM(i, i)];
+        }
+        za[0] = z[0]; za[1] = z[1]; za[2] = z[2]; zb[0] = z[3]; zb[1] = z[4]; zb[2] = z[5];
+    }
+    __syncwarp();
+    if (lane < 6) {
+        T s = 0;
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            const T* y = F + A_TK + 18 * k + 3 * lane; const T* z = E.xv + 6 + 3 * k;
+            s += y[0] * z[0] + y[1] * z[1] + y[2] * z[2];
+        }
+        E.xv[lane] -= s;
+    }
+    __syncwarp();
+    T x[6];
+#pragma unroll
+    for (int i = 0; i < 6; i++) x[i] = E.xv[i];
+    solve6(F, x);
+    __syncwarp();
+    if (lane >= 6 && lane < NDOF) {
+        const int k = (lane - 6) / 3, i = lane - 6 - 3 * k;
+        T z = E.xv[lane];
+#pragma unroll
+        for (int j = 0; j < 6; j++) z -= F[A_TK + 18 * k + 3 * j + i] * x[j];
+        E.xv[lane] = z;
+    }
+    if (lane == 0) {
+#pragma unroll
+        for (int i = 0; i < 6; i++) E.xv[i] = x[i];
+    }
+    __syncwarp();
+    if (lane < 4 && lane != la && lane != lb) {
+        const T* l = F + A_KK + 6 * lane; T* z = E.xv + 6 + 3 * lane;
+        const T w2 = z[2] * l[5];
+        const T w1 = (z[1] - l[4] * w2) * l[2];
+        const T w0 = (z[0] - l[1] * w1 - l[3] * w2) * l[0];
+        z[0] = w0; z[1] = w1; z[2] = w2;
+    } else if (lane == 4) {
+        T* za = E.xv + 6 + 3 * la; T* zb = E.xv + 6 + 3 * lb;
+        T z[6] = {za[0], za[1], za[2], zb[0], zb[1], zb[2]};
+#pragma unroll
+        for (int i = 5; i >= 0; i--) {
+            T s = z[i];
+#pragma unroll
+            for (int k = i + 1; k < 6; k++) s -= G[SYM(k, i)] * z[k];
+            z[i] = s * G[SYM(i, i)];
+        }
+        za[0] = z[0]; za[1] = z[1]; za[2] = z[2]; zb[0] = z[3]; zb[1] = z[4]; zb[2] = z[5];
+    }
+    __syncwarp();
+    const T r = lane < NDOF ? E.xv[lane] : T(0);
+    __syncwarp();
+    return r;
+}
+
 // ---- environments with a leg-leg contact: the 12 x 12 leg block KD = E.kd() is dense (pair_hessian), the trunk block tt and the
 // couplings tk stay in the arrow storage A.  Same elimination order as arrow_factor: KD = L L' (in place, diagonals inverted),
 // tk -> Y = C L^-T, tt -> Cholesky factor of the Schur complement tt - Y Y'.
@@ -604,6 +749,7 @@ struct EnvCfg {
     int biped;
     T biped_w[10], biped_reset_z, biped_reset_qw, biped_reset_qy, foot_site[2][3];
     const T* biped_ready;      // device array [12] (indexed by lane: kept out of the kernel parameters, which must not be indexed dynamically)
+    const unsigned char* gp_tab;   // device: candidate geom pairs of the robot-robot collision, a[NGP] then b[NGP] (DevModel::gp_a / gp_b)
 };
 
 // kinematic quantities the biped terms read from mjData (world frame, start of the last substep), one row per env
@@ -928,29 +1074,99 @@ GO1_DEV bool contact_stiffness(const DevModel<T>& m, WEnv<T>& E, int lane) {
     return true;
 }
 
-// Hessian terms of the robot-robot contacts in the bottom / middle zone.  Both bodies ride on the trunk, so the rows
-// J = G (S_body2 - S_body1) are zero on the six trunk dofs: the terms live in the 12 x 12 leg block.  Contacts within one
-// leg, or between a leg and the trunk, stay inside that leg's 3x3 block of the block-arrow matrix (return 1, added to
-// E.H).  A contact between two legs fills the off-diagonal 3x3 block: the leg block becomes dense (return 2, complete
-// 12 x 12 block in E.kd(); dense_factor / dense_solve).  Returns 0 when no such contact is active.  E.H must hold the arrow.
+// Jacobian rows of robot-robot contact c restricted to the 12 leg dofs: JB[j * 12 + u] = J_j[6 + u] (lanes u < 12).  Both bodies ride
+// on the trunk, so J = G (S_body2 - S_body1) is zero on the six trunk dofs.
+template <typename T>
+GO1_DEV void pair_jacobian(const DevModel<T>& m, WEnv<T>& E, int c, int meta, int dim, T* JB, int lane) {
+    if (lane < 12) {
+        const int b2 = meta_b2(meta), b1 = meta_b1p(meta) - 1;
+        const int k = lane / 3, i = lane - 3 * k;          // dof 6 + lane moves body b iff b is link >= i of leg k
+        const bool m2 = b2 >= 1 && (b2 - 1) / 3 == k && (b2 - 1) - 3 * k >= i;
+        const bool m1 = b1 >= 1 && (b1 - 1) / 3 == k && (b1 - 1) - 3 * k >= i;
+        const T sgn = (m2 ? T(1) : T(0)) - (m1 ? T(1) : T(0));
+        T F[9], cd[6];
+        contact_frame(m, E, c, dim, F);
+        const T r[3] = {E.c_r[0][c], E.c_r[1][c], E.c_r[2][c]};
+#pragma unroll
+        for (int e = 0; e < 6; e++) cd[e] = E.cdof[6 + lane][e];
+#pragma unroll
+        for (int j = 0; j < 3; j++) {
+            T cr[3];
+            cross3(cr, r, F + 3 * j);
+            JB[j * 12 + lane] = j < dim ? sgn * (dot3(cr, cd) + dot3(F + 3 * j, cd + 3)) : T(0);
+            JB[(3 + j) * 12 + lane] = dim == 6 ? sgn * dot3(F + 3 * j, cd) : T(0);
+        }
+    }
+    __syncwarp();
+}
+
+// Hessian terms J' Hc J of the robot-robot contacts in the bottom / middle zone; they live in the 12 x 12 leg block.  E.H must
+// hold the arrow.  Returns
+//   0  no such contact is active
+//   1  only contacts inside one leg or between a leg and the trunk: added to the legs' 3x3 blocks of E.H (still block-arrow)
+//   2 | (4 la + lb) << 2   exactly one pair of legs la < lb is coupled: their 6 dofs form one dense 6x6 block, packed in E.g6()
+//      (pairleg_factor / pairleg_solve); the 3x3 blocks of E.H hold the diagonal parts
+//   3  several leg pairs are coupled: complete dense 12 x 12 leg block in E.kd() (dense_factor / dense_solve)
 template <typename T>
 GO1_NOINL int pair_hessian(const DevModel<T>& m, WEnv<T>& E, int lane) {
     const int nfl = E.nfl, ncon = E.ncon;
-    bool any = false, cross = false;
+    bool any = false;
+    int code = -1;                                     // 4 * min(leg) + max(leg) of an active leg-leg contact (PW <= 32: one per lane)
     for (int c = nfl + lane; c < ncon; c += 32) {
         if (E.c_s[13][c] != 0) {
             any = true;
             const int meta = E.c_meta[c];
             const int b2 = meta_b2(meta), b1 = meta_b1p(meta) - 1;
-            cross |= b1 >= 1 && b2 >= 1 && (b1 - 1) / 3 != (b2 - 1) / 3;
+            if (b1 >= 1 && b2 >= 1) {
+                const int l1 = (b1 - 1) / 3, l2 = (b2 - 1) / 3;
+                if (l1 != l2) code = l1 < l2 ? 4 * l1 + l2 : 4 * l2 + l1;
+            }
         }
     }
     if (!__any_sync(FULL, any)) return 0;
-    const bool dense = __any_sync(FULL, cross);
-    T* KD = E.kd();
+    const unsigned cm = __ballot_sync(FULL, code >= 0);
+    int first = -1;
+    bool multi = false;
+    if (cm) {
+        first = __shfl_sync(FULL, code, __ffs((int)cm) - 1);
+        multi = __any_sync(FULL, code >= 0 && code != first);
+    }
     T* JB = E.jbuf();
+    if (multi) {
+        T* KD = E.kd();
 #pragma unroll 1
-    for (int idx = lane; idx < 144; idx += 32) KD[idx] = 0;
+        for (int idx = lane; idx < 144; idx += 32) KD[idx] = 0;
+        __syncwarp();
+#pragma unroll 1
+        for (int c = nfl; c < ncon; c++) {
+            const int zone = (int)E.c_s[13][c];
+            if (zone == 0) continue;
+            const int meta = E.c_meta[c];
+            const DevClass<T>& cl = m.cls[meta_cls(meta)];
+            pair_jacobian(m, E, c, meta, cl.dim, JB, lane);
+            const T D0 = E.c_D0[c];
+#pragma unroll 1
+            for (int idx = lane; idx < 144; idx += 32) {
+                const int u = idx / 12, v = idx - 12 * u;
+                T gx[6], gy[6];
+#pragma unroll
+                for (int j = 0; j < 6; j++) { gx[j] = JB[j * 12 + u]; gy[j] = JB[j * 12 + v]; }
+                KD[idx] += cone_quad(cl, E, c, zone, D0, gx, gy);
+            }
+            __syncwarp();
+        }
+        if (lane < 24) {
+            const int k = lane / 6, e = lane - 6 * k;
+            const int i = m.tab.sym_r[e], cc = m.tab.sym_c[e];
+            const T hv = E.H[A_KK + 6 * k + e];
+            KD[(3 * k + i) * 12 + 3 * k + cc] += hv;
+            if (i != cc) KD[(3 * k + cc) * 12 + 3 * k + i] += hv;
+        }
+        __syncwarp();
+        return 3;
+    }
+    T* X = E.g6() + 21;                                 // 3x3 coupling block (rows: leg lb, columns: leg la)
+    if (first >= 0 && lane < 9) X[lane] = 0;
     __syncwarp();
 #pragma unroll 1
     for (int c = nfl; c < ncon; c++) {
@@ -958,50 +1174,43 @@ GO1_NOINL int pair_hessian(const DevModel<T>& m, WEnv<T>& E, int lane) {
         if (zone == 0) continue;
         const int meta = E.c_meta[c];
         const DevClass<T>& cl = m.cls[meta_cls(meta)];
-        const int dim = cl.dim;
-        if (lane < 12) {
-            const int b2 = meta_b2(meta), b1 = meta_b1p(meta) - 1;
-            const int k = lane / 3, i = lane - 3 * k;          // dof 6 + lane moves body b iff b is link >= i of leg k
-            const bool m2 = b2 >= 1 && (b2 - 1) / 3 == k && (b2 - 1) - 3 * k >= i;
-            const bool m1 = b1 >= 1 && (b1 - 1) / 3 == k && (b1 - 1) - 3 * k >= i;
-            const T sgn = (m2 ? T(1) : T(0)) - (m1 ? T(1) : T(0));
-            T F[9], cd[6];
-            contact_frame(m, E, c, dim, F);
-            const T r[3] = {E.c_r[0][c], E.c_r[1][c], E.c_r[2][c]};
-#pragma unroll
-            for (int e = 0; e < 6; e++) cd[e] = E.cdof[6 + lane][e];
-#pragma unroll
-            for (int j = 0; j < 3; j++) {
-                T cr[3];
-                cross3(cr, r, F + 3 * j);
-                JB[j * 12 + lane] = j < dim ? sgn * (dot3(cr, cd) + dot3(F + 3 * j, cd + 3)) : T(0);
-                JB[(3 + j) * 12 + lane] = dim == 6 ? sgn * dot3(F + 3 * j, cd) : T(0);
+        pair_jacobian(m, E, c, meta, cl.dim, JB, lane);
+        const int b2 = meta_b2(meta), b1 = meta_b1p(meta) - 1;
+        const int l2 = b2 >= 1 ? (b2 - 1) / 3 : -1, l1 = b1 >= 1 ? (b1 - 1) / 3 : -1;
+        const bool two = l1 >= 0 && l2 >= 0 && l1 != l2;
+        const int ka = two ? (l1 < l2 ? l1 : l2) : (l2 >= 0 ? l2 : l1), kb = two ? (l1 < l2 ? l2 : l1) : -1;
+        // lanes 0..5: 3x3 block of leg ka; 6..11: leg kb; 12..20: coupling block (row in kb, column in ka)
+        if (lane < 6 || (two && lane < 21)) {
+            int u, v;
+            T* dst;
+            if (lane < 12) {
+                const int k = lane < 6 ? ka : kb, e = lane < 6 ? lane : lane - 6;
+                u = 3 * k + m.tab.sym_r[e]; v = 3 * k + m.tab.sym_c[e];
+                dst = E.H + A_KK + 6 * k + e;
+            } else {
+                const int e = lane - 12, i = e / 3;
+                u = 3 * kb + i; v = 3 * ka + (e - 3 * i);
+                dst = X + e;
             }
-        }
-        __syncwarp();
-        const T D0 = E.c_D0[c];
-#pragma unroll 1
-        for (int idx = lane; idx < 144; idx += 32) {
-            const int u = idx / 12, v = idx - 12 * u;
             T gx[6], gy[6];
 #pragma unroll
             for (int j = 0; j < 6; j++) { gx[j] = JB[j * 12 + u]; gy[j] = JB[j * 12 + v]; }
-            KD[idx] += cone_quad(cl, E, c, zone, D0, gx, gy);
+            *dst += cone_quad(cl, E, c, zone, E.c_D0[c], gx, gy);
         }
         __syncwarp();
     }
-    if (lane < 24) {
-        const int k = lane / 6, e = lane - 6 * k;
-        const int i = m.tab.sym_r[e], cc = m.tab.sym_c[e];
-        if (!dense) E.H[A_KK + 6 * k + e] += KD[(3 * k + i) * 12 + 3 * k + cc];
-        else {
-            const T hv = E.H[A_KK + 6 * k + e];
-            KD[(3 * k + i) * 12 + 3 * k + cc] += hv;
-            if (i != cc) KD[(3 * k + cc) * 12 + 3 * k + i] += hv;
-        }
+    if (first < 0) return 1;
+    const int la = first >> 2, lb = first & 3;
+    if (lane < 21) {
+        const int r = m.tab.sym_r[lane], cc = m.tab.sym_c[lane];
+        T v;
+        if (r < 3) v = E.H[A_KK + 6 * la + SYM(r, cc)];
+        else if (cc >= 3) v = E.H[A_KK + 6 * lb + SYM(r - 3, cc - 3)];
+        else v = X[(r - 3) * 3 + cc];
+        E.g6()[lane] = v;
     }
     __syncwarp();
-    return dense ? 2 : 1;
+    return 2 | (first << 2);
 }
 
 // line-search polynomials of every contact for the direction whose body-space image is E.bv[1] (S), at the
@@ -1313,88 +1522,101 @@ GO1_NOINL void substep_w(const DevModel<T>& m, const EnvCfg<T>& cfg, WEnv<T>& E,
             while (lo < hi) { const int mid = (lo + hi) >> 1; if (meta_b2(E.c_meta[mid]) < lane) lo = mid + 1; else hi = mid; }
             E.bstart[lane] = lo;
         }
-        // ---- robot-robot pairs (mj_collision body pairs in (body1, body2) order; go1_pair.cuh).  The body frames are still in
-        // the Kc words; the centres of the bodies' bounding spheres go to the (dead) contact scratch.
+        GO1_PB();      // F1
+        // ---- robot-robot pairs (go1_pair.cuh).  Candidate geom pairs come from a table in (body1, body2, geom1, geom2) order --
+        // mj_collision's order: bodies that are parent and child, geoms of one body and hip-motor pairs are not in it.  Pass 1:
+        // bounding-sphere test of every table entry, the hits are compacted (order kept).  Pass 2: one lane per hit runs the
+        // narrowphase.  The body frames are still in the Kc words; geom centres and the hit list use the (dead) contact scratch.
         int nall = nfl;
 #if GO1_SELF_COLLISION
         {
-            T* bc = &E.c_s[0][0];
-            if (lane < NB) {
+            constexpr int MAXHIT = 64;
+            T* gc = &E.c_s[0][0];
+            int* hits = reinterpret_cast<int*>(gc + 3 * GFLAT);
+#pragma unroll 1
+            for (int g = lane; g < m.nflat; g += 32) {
+                const DevGeom<T>& G = m.flat[g];
                 T cw[3];
-                matvec3(cw, E.xmat()[lane], m.bsph[lane]);
+                matvec3(cw, E.xmat()[G.slot], G.pos);
 #pragma unroll
-                for (int e = 0; e < 3; e++) bc[3 * lane + e] = cw[e] + E.xpos()[lane][e];
+                for (int e = 0; e < 3; e++) gc[3 * g + e] = cw[e] + E.xpos()[G.slot][e];
             }
             __syncwarp();
+            const unsigned char* gpa = cfg.gp_tab;
+            const unsigned char* gpb = cfg.gp_tab + NGP;
             const T pmargin = m.pair_margin;
+            int nhit = 0;
 #pragma unroll 1
-            for (int p0 = 0; p0 < m.npairs; p0 += 32) {
+            for (int p0 = 0; p0 < m.ngp; p0 += 32) {
                 const int pi = p0 + lane;
                 bool hit = false;
-                if (pi < m.npairs) {
-                    const int a = m.pair_a[pi], b = m.pair_b[pi];
-                    const T d[3] = {bc[3 * a] - bc[3 * b], bc[3 * a + 1] - bc[3 * b + 1], bc[3 * a + 2] - bc[3 * b + 2]};
-                    const T bound = m.bsph[a][3] + m.bsph[b][3] + pmargin;
+                if (pi < m.ngp) {
+                    const int a = gpa[pi], b = gpb[pi];
+                    const T d[3] = {gc[3 * a] - gc[3 * b], gc[3 * a + 1] - gc[3 * b + 1], gc[3 * a + 2] - gc[3 * b + 2]};
+                    const T bound = m.flat_rb[a] + m.flat_rb[b] + pmargin;
                     hit = dot3(d, d) <= bound * bound;
                 }
-                unsigned mask = __ballot_sync(FULL, hit);
-#pragma unroll 1
-                while (mask) {
-                    const int pj = p0 + __ffs((int)mask) - 1;
-                    mask &= mask - 1;
-                    const int a = m.pair_a[pj], b = m.pair_b[pj];
-                    const int ga0 = m.body_g0[a], na = m.body_g0[a + 1] - ga0, gb0 = m.body_g0[b], nb = m.body_g0[b + 1] - gb0;
-                    Stage2<T> st;
-                    st.cnt = 0;
-#pragma unroll
-                    for (int k = 0; k < 3; k++) { st.p[0][k] = st.p[1][k] = st.n[0][k] = st.n[1][k] = 0; }
-                    st.d[0] = st.d[1] = 0;
-                    int meta = 0;
-                    if (lane < na * nb) {
-                        const int ia = lane / nb, ib = lane - ia * nb;
-                        int g1 = ga0 + ia, g2 = gb0 + ib;           // flat indices; geom1 = the lower geom type (mj_collideGeoms)
-                        if (m.flat[g1].type > m.flat[g2].type) { const int t_ = g1; g1 = g2; g2 = t_; }
-                        GeomW<T> w1, w2;
-#pragma unroll
-                        for (int q = 0; q < 2; q++) {
-                            const DevGeom<T>& g = m.flat[q == 0 ? g1 : g2];
-                            GeomW<T>& w = q == 0 ? w1 : w2;
-                            const T* Rg = E.xmat()[g.slot];
-                            w.type = g.type;
-                            matvec3(w.c, Rg, g.pos);
-                            matvec3(w.z, Rg, g.zax);
-                            matvec3(w.x, Rg, g.xax);
-#pragma unroll
-                            for (int k = 0; k < 3; k++) { w.c[k] += E.xpos()[g.slot][k]; w.s[k] = g.size[k]; }
-                        }
-                        const DevGeom<T>& G1 = m.flat[g1]; const DevGeom<T>& G2 = m.flat[g2];
-                        const int ci = m.pair_cls[G1.kind][G2.kind];
-                        const T margin = m.cls[ci].margin, inc = m.cls[ci].incmargin;
-                        const T dd[3] = {w2.c[0] - w1.c[0], w2.c[1] - w1.c[1], w2.c[2] - w1.c[2]};
-                        const T bound = m.flat_rb[g1] + m.flat_rb[g2] + margin;
-                        if (dot3(dd, dd) <= bound * bound) pp_collide(w1, w2, margin, inc, st);
-                        meta = G2.slot | ((G1.slot + 1) << 4) | (ci << 8) | (G2.gid << 16) | (G1.gid << 22);
-                    }
-                    int cnt = st.cnt < 2 ? st.cnt : 2;
-                    int incl = cnt;
-#pragma unroll
-                    for (int d = 1; d < 32; d <<= 1) { const int v = __shfl_up_sync(FULL, incl, d); if (lane >= d) incl += v; }
-                    const int total = __shfl_sync(FULL, incl, 31);
-                    const int off = nall + incl - cnt;
-#pragma unroll
-                    for (int j = 0; j < 2; j++) {
-                        const int c = off + j;
-                        if (j < cnt && c < CW && c - nfl < PW) {
-                            E.c_r[0][c] = st.p[j][0] - com[0]; E.c_r[1][c] = st.p[j][1] - com[1]; E.c_r[2][c] = st.p[j][2] - com[2];
-                            E.c_D0[c] = st.d[j]; E.c_meta[c] = meta;
-                            E.c_n[0][c - nfl] = st.n[j][0]; E.c_n[1][c - nfl] = st.n[j][1]; E.c_n[2][c - nfl] = st.n[j][2];
-                        }
-                    }
-                    nall += total;
+                const unsigned mask = __ballot_sync(FULL, hit);
+                if (hit) {
+                    const int k = nhit + __popc(mask & ((1u << lane) - 1u));
+                    if (k < MAXHIT) hits[k] = pi;
                 }
+                nhit += __popc(mask);
             }
-            int cap = nfl + PW < CW ? nfl + PW : CW;
+            __syncwarp();
+            if (nhit > MAXHIT) { nover += nhit - MAXHIT; nhit = MAXHIT; }
+#pragma unroll 1
+            for (int h0 = 0; h0 < nhit; h0 += 32) {
+                Stage2<T> st;
+                st.cnt = 0;
+#pragma unroll
+                for (int k = 0; k < 3; k++) { st.p[0][k] = st.p[1][k] = st.n[0][k] = st.n[1][k] = 0; }
+                st.d[0] = st.d[1] = 0;
+                int meta = 0;
+                if (h0 + lane < nhit) {
+                    const int pi = hits[h0 + lane];
+                    int g1 = gpa[pi], g2 = gpb[pi];             // flat indices; geom1 = the lower geom type (mj_collideGeoms)
+                    if (m.flat[g1].type > m.flat[g2].type) { const int t_ = g1; g1 = g2; g2 = t_; }
+                    GeomW<T> w1, w2;
+#pragma unroll
+                    for (int q = 0; q < 2; q++) {
+                        const int gq = q == 0 ? g1 : g2;
+                        const DevGeom<T>& g = m.flat[gq];
+                        GeomW<T>& w = q == 0 ? w1 : w2;
+                        const T* Rg = E.xmat()[g.slot];
+                        w.type = g.type;
+                        matvec3(w.z, Rg, g.zax);
+                        matvec3(w.x, Rg, g.xax);
+#pragma unroll
+                        for (int k = 0; k < 3; k++) { w.c[k] = gc[3 * gq + k]; w.s[k] = g.size[k]; }
+                    }
+                    const DevGeom<T>& G1 = m.flat[g1]; const DevGeom<T>& G2 = m.flat[g2];
+                    const int ci = m.pair_cls[G1.kind][G2.kind];
+                    pp_collide(w1, w2, m.cls[ci].margin, m.cls[ci].incmargin, st);
+                    meta = G2.slot | ((G1.slot + 1) << 4) | (ci << 8) | (G2.gid << 16) | (G1.gid << 22);
+                }
+                const int cnt = st.cnt < 2 ? st.cnt : 2;
+                int incl = cnt;
+#pragma unroll
+                for (int d = 1; d < 32; d <<= 1) { const int v = __shfl_up_sync(FULL, incl, d); if (lane >= d) incl += v; }
+                const int total = __shfl_sync(FULL, incl, 31);
+                const int off = nall + incl - cnt;
+#pragma unroll
+                for (int j = 0; j < 2; j++) {
+                    const int c = off + j;
+                    if (j < cnt && c < CW && c - nfl < PW) {
+                        E.c_r[0][c] = st.p[j][0] - com[0]; E.c_r[1][c] = st.p[j][1] - com[1]; E.c_r[2][c] = st.p[j][2] - com[2];
+                        E.c_D0[c] = st.d[j]; E.c_meta[c] = meta;
+                        E.c_n[0][c - nfl] = st.n[j][0]; E.c_n[1][c - nfl] = st.n[j][1]; E.c_n[2][c - nfl] = st.n[j][2];
+                    }
+                }
+                nall += total;
+            }
+            const int cap = nfl + PW < CW ? nfl + PW : CW;
             if (nall > cap) { nover += nall - cap; nall = cap; }
+#if GO1_SELF_COLLISION == 2
+            nall = nfl;      // timing experiment only: collision phase executed, contacts discarded
+#endif
         }
 #endif
         __syncwarp();
@@ -1402,6 +1624,7 @@ GO1_NOINL void substep_w(const DevModel<T>& m, const EnvCfg<T>& cfg, WEnv<T>& E,
         __syncwarp();
     }
     ncon = E.ncon;
+    GO1_PB();          // F2
     // ------------------------------------------------------------------ mj_crb -> block-arrow M (+ armature)
     composite10(E.crb, lane);
     composite21(m, E.Kc, E.crb, false, lane);          // (overwrites xmat / xpos: collision is done)
@@ -1515,7 +1738,7 @@ GO1_NOINL void substep_w(const DevModel<T>& m, const EnvCfg<T>& cfg, WEnv<T>& E,
         if (capture && lane == 0) con_out[0] = (T)ncon;
     }
     __syncwarp();
-    }   // active
+    } else { GO1_PB(); GO1_PB(); }   // active
     // ------------------------------------------------------------------ mj_fwdConstraint: warmstart + Newton
     T a = as_, Ma = qfs, qfc = 0, hdiag = 0, grad = 0, cost = 0, oldcost = 0;
     const T scale = T(1) / (m.meaninertia * T(18));
@@ -1547,7 +1770,7 @@ GO1_NOINL void substep_w(const DevModel<T>& m, const EnvCfg<T>& cfg, WEnv<T>& E,
 #else
         if (conv) break;
 #endif
-        if (conv) continue;
+        if (conv) { GO1_PB3(); continue; }
         do {
         if (lane < NDOF) E.xv[lane] = a;
         __syncwarp();
@@ -1568,6 +1791,7 @@ GO1_NOINL void substep_w(const DevModel<T>& m, const EnvCfg<T>& cfg, WEnv<T>& E,
             __syncwarp();
             Ma = arrow_matvec(E, E.M, lane);
             __syncwarp();
+            GO1_PB3();
             break;
         }
         if (phase == 1) {
@@ -1578,6 +1802,7 @@ GO1_NOINL void substep_w(const DevModel<T>& m, const EnvCfg<T>& cfg, WEnv<T>& E,
                 __syncwarp();
                 Ma = arrow_matvec(E, E.M, lane);
                 __syncwarp();
+                GO1_PB3();
                 break;
             }
         }
@@ -1593,22 +1818,23 @@ GO1_NOINL void substep_w(const DevModel<T>& m, const EnvCfg<T>& cfg, WEnv<T>& E,
         first = false;
         cost = cnew;
 #ifdef GO1_DBG_FIXED_ITERS
-        if (iter >= GO1_DBG_FIXED_ITERS) { conv = true; break; }      // timing experiment only: same trip count everywhere
+        if (iter >= GO1_DBG_FIXED_ITERS) { conv = true; GO1_PB3(); break; }      // timing experiment only: same trip count everywhere
 #else
-        if (iter >= maxiter) { conv = true; break; }
+        if (iter >= maxiter) { conv = true; GO1_PB3(); break; }
         // MuJoCo's exit test (after >= 1 move): gradient small, or improvement small.  The measured improvement is a
         // difference of O(cost) numbers and is pure rounding noise in fp32 once it drops below ~1e-7*cost, so
         // "improvement small" is only trusted when the Newton decrement -g.s/2 (the predicted improvement of the
         // next move, free of cancellation) is small too; see DESIGN.md.
-        if (iter > 0 && gradient < tol) { conv = true; break; }
+        if (iter > 0 && gradient < tol) { conv = true; GO1_PB3(); break; }
         // fp32: |grad| never reaches MuJoCo's 1e-8 (rounding floor of M a - qfrc), but H >= M >= lambda_lb*I bounds the Newton
         // decrement from the gradient alone: g'H^-1 g / 2 <= |g|^2 / (2 lambda_lb).  If even that bound is below the
         // tolerance the point is converged and the Hessian assembly / factorisation / solve of this round are skipped.
         if (GO1_GRAD_BOUND_EXIT && sizeof(T) == 4 && iter > 0 && m.lambda_lb > 0 &&
-            T(0.5) * gradient * gradient < tol * scale * m.lambda_lb) { conv = true; break; }
-        if (nstall >= 3) { conv = true; break; }
+            T(0.5) * gradient * gradient < tol * scale * m.lambda_lb) { conv = true; GO1_PB3(); break; }
+        if (nstall >= 3) { conv = true; GO1_PB3(); break; }
 #endif
         // ---- Hessian H = M + J'DJ (+ cone blocks), block-arrow; search = -H^-1 grad
+        GO1_PB();      // B1
         if (contact_stiffness(m, E, lane)) {
             composite21(m, E.Kc, E.crb, true, lane);
             assemble_arrow(m, E, E.Kc, E.H, lane);
@@ -1622,10 +1848,18 @@ GO1_NOINL void substep_w(const DevModel<T>& m, const EnvCfg<T>& cfg, WEnv<T>& E,
         __syncwarp();
         // robot-robot contacts (rare): inside one leg block, or leg-leg fill -> dense 12 x 12 leg block
         const int pmode = E.ncon > E.nfl ? pair_hessian(m, E, lane) : 0;
+#ifdef GO1_EMU_COUNT
+        if (lane == 0) { __atomic_fetch_add(&g_emu_rounds[pmode & 3], 1, __ATOMIC_RELAXED); if (E.ncon > E.nfl) __atomic_fetch_add(&g_emu_rounds[3], 1, __ATOMIC_RELAXED); }
+#endif
+        GO1_PB();      // B2
         T s;
-        if (pmode == 2) {
+        if ((pmode & 3) == 3) {
             dense_factor(E, m, E.H, lane);
             s = -dense_solve(E, E.H, grad, lane);
+        } else if ((pmode & 3) == 2) {
+            const int la = pmode >> 4, lb = (pmode >> 2) & 3;
+            pairleg_factor(E, m, E.H, la, lb, lane);
+            s = -pairleg_solve(E, E.H, grad, la, lb, lane);
         } else {
             arrow_factor(m, E.H, lane);
             s = -arrow_solve(E, E.H, grad, lane);
@@ -1637,10 +1871,11 @@ GO1_NOINL void substep_w(const DevModel<T>& m, const EnvCfg<T>& cfg, WEnv<T>& E,
         if ((GO1_DEC_EXIT && sizeof(T) == 4 && (iter > 0 || GO1_DEC_EXIT > 1)) || (iter > 0 && improvement < tol)) {
             const T dec = warp_sum(grad * s);
 #ifndef GO1_DBG_FIXED_ITERS
-            if (T(-0.5) * scale * dec < tol) { conv = true; break; }
+            if (T(-0.5) * scale * dec < tol) { conv = true; GO1_PB(); break; }
 #endif
         }
         // ---- exact line search (PrimalSearch)
+        GO1_PB();      // B3
         if (lane < NDOF) E.xv[lane] = s;
         __syncwarp();
         const T Ms = arrow_matvec(E, E.M, lane);

@@ -16,6 +16,7 @@
 #define GO1_LAUNCH(kernel, grid, block, smem, stream, ...) kernel<<<grid, block, smem, stream>>>(__VA_ARGS__)
 #endif
 #include <cmath>
+#include <cstddef>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -201,12 +202,12 @@ GO1_DEV void reset_env(const DevModel<T>& m, const EnvCfg<T>& cfg, WEnv<T>& E, i
 template <typename T>
 __global__ void __launch_bounds__(GO1_WARPS * 32, GO1_MINBLOCKS) k_step(const __grid_constant__ KParams<T> P) {
     GO1_DYN_SMEM(smem_raw);
-    constexpr size_t MODEL_BYTES = (sizeof(DevModel<T>) + 15) & ~size_t(15);
+    constexpr size_t MODEL_BYTES = (offsetof(DevModel<T>, gp_a) + 15) & ~size_t(15);      // the geom-pair table stays in global memory
     DevModel<T>& m = *reinterpret_cast<DevModel<T>*>(smem_raw);
     {
         const int* src = reinterpret_cast<const int*>(P.model);
         int* dst = reinterpret_cast<int*>(smem_raw);
-        for (int i = threadIdx.x; i < (int)(sizeof(DevModel<T>) / 4); i += blockDim.x) dst[i] = src[i];
+        for (int i = threadIdx.x; i < (int)((offsetof(DevModel<T>, gp_a) + 3) / 4); i += blockDim.x) dst[i] = src[i];
     }
     __syncthreads();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -548,6 +549,21 @@ __global__ void k_order(const int* __restrict__ work, int* __restrict__ order, i
     for (int i = threadIdx.x; i < n; i += blockDim.x) { int k = work[i]; k = k < 0 ? 0 : (k > 255 ? 255 : k); order[atomicAdd(&hist[255 - k], 1)] = i; }
 }
 
+// Spreads the episode phases of a slab that was reset all at once (bench / throughput runs): an environment that is currently
+// unhealthy gets its consecutive-unhealthy-step counter (go1_mujoco_env.py:487-493) set to a Philox draw in [0, max_unhealthy],
+// so that terminations arrive at a uniform rate instead of all at control step ~800.  Nothing else of the state changes.
+__global__ void k_stagger(int* __restrict__ sint, int n, int max_unhealthy, unsigned long long seed, unsigned long long env_offset) {
+    const int e = blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= n) return;
+    int* si = sint + (size_t)e * I_STRIDE;
+    if (si[I_UNHEALTHY] <= 0) return;
+    const unsigned long long gid = env_offset + (unsigned long long)e;
+    const U4 r = philox(seed ^ 0x5354414747455221ull, (unsigned)gid, (unsigned)(gid >> 32), 0u, 0x53544752u);
+    const int k = (int)(r.x % (unsigned)(max_unhealthy + 1));
+    si[I_UNHEALTHY] = k;
+    if (si[I_STEP] < k) si[I_STEP] = k;
+}
+
 // 48-64-64-12 tanh MLP + Gaussian sampling + clip: one thread per env (weights in shared memory).
 // Round-1 version on the FP32 pipe; the tensor-core (tcgen05) version is tracked in DESIGN.md "next".
 __global__ void __launch_bounds__(128) k_policy(const float* __restrict__ obs, float* __restrict__ act, int n, Go1Policy pol,
@@ -620,7 +636,7 @@ struct Go1Sim {
 static std::string g_create_err;
 
 static size_t step_smem_bytes() {
-    return ((sizeof(DevModel<real>) + 15) & ~size_t(15)) + sizeof(WEnv<real>) * GO1_WARPS;
+    return ((offsetof(DevModel<real>, gp_a) + 15) & ~size_t(15)) + sizeof(WEnv<real>) * GO1_WARPS;
 }
 
 #define CK(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { h->err = std::string(#call) + ": " + cudaGetErrorString(e_); return GO1_ECUDA; } } while (0)
@@ -673,6 +689,7 @@ static void fill_cfg(EnvCfg<real>& k, const Go1EnvConfig& c, const DevModel<doub
     const double bwd[10] = {15.0, 50.0, 5.0, 8.0, 5.0, 9.0, 6.0, 0.7, 150.0, 25.0};
     for (int i = 0; i < 10; i++) k.biped_w[i] = (real)(c.biped_w[i] == def.biped_w[i] ? bwd[i] : (double)c.biped_w[i]);
     k.biped_ready = nullptr;   // device copy made by go1_create
+    k.gp_tab = nullptr;        // points into the device model (go1_create)
     k.biped_reset_z = (real)(c.biped_reset_z == def.biped_reset_z ? 0.65 : (double)c.biped_reset_z);
     const double half = 0.5 * (double)c.biped_reset_pitch_deg * (3.14159265358979323846 / 180.0);     // np.deg2rad(-95) / 2 (:970-971)
     k.biped_reset_qw = (real)std::cos(half); k.biped_reset_qy = (real)std::sin(half);
@@ -706,6 +723,7 @@ int go1_create(const void* model_blob, size_t nbytes, const Go1EnvConfig* cfg_in
     e = cudaMemcpy(h->dmodel, hm, sizeof(DevModel<real>), cudaMemcpyHostToDevice);
     delete hm;
     if (e != cudaSuccess) return fail("cudaMemcpy model", e);
+    h->cfg.gp_tab = reinterpret_cast<const unsigned char*>(h->dmodel) + offsetof(DevModel<real>, gp_a);
     const size_t N = (size_t)n_envs;
 #define ALLOC(p, bytes) if ((e = cudaMalloc((void**)&(p), (bytes))) != cudaSuccess) return fail("cudaMalloc " #p, e); cudaMemset((p), 0, (bytes))
     ALLOC(h->sreal, sizeof(real) * S_STRIDE * N); ALLOC(h->sint, sizeof(int) * I_STRIDE * N);
@@ -951,6 +969,19 @@ int go1_rollout(go1_handle h, int n_steps, int action_mode, const Go1Policy* pol
     return GO1_OK;
 }
 
+int go1_stagger_phases(go1_handle h) {
+    if (!h) return GO1_EINVAL;
+    CK(cudaSetDevice(h->device));
+#ifdef GO1_EMU
+    GO1_LAUNCH(k_stagger, h->n_envs, 1, 0, h->stream, h->sint, h->n_envs, h->cfg.max_unhealthy_steps, h->seed, h->env_offset);
+#else
+    GO1_LAUNCH(k_stagger, (h->n_envs + 255) / 256, 256, 0, h->stream, h->sint, h->n_envs, h->cfg.max_unhealthy_steps, h->seed, h->env_offset);
+#endif
+    CK(cudaGetLastError());
+    CK(cudaStreamSynchronize(h->stream));
+    return GO1_OK;
+}
+
 int go1_policy_act(go1_handle h, const Go1Policy* policy, const float* obs_dev, float* act_dev, int n, void* stream) {
     if (!h || !policy || !obs_dev || !act_dev || n < 0) return GO1_EINVAL;
     CK(cudaSetDevice(h->device));
@@ -1117,3 +1148,8 @@ int go1_get_attr_f32(go1_handle h, const char* name, float* v) {
 }
 
 }  // extern "C"
+
+#ifdef GO1_EMU_COUNT
+long g_emu_rounds[4] = {0, 0, 0, 0};      // test-only instrumentation of the emulator build: Newton rounds by Hessian path
+extern "C" void go1_emu_round_counts(long* out) { for (int i = 0; i < 4; i++) out[i] = g_emu_rounds[i]; }
+#endif

@@ -76,7 +76,7 @@ EXPORTS = (
     "go1_num_envs", "go1_action_bounds", "go1_reset", "go1_step", "go1_step_host", "go1_reset_host", "go1_rollout", "go1_policy_act",
     "go1_last_rollout_timing", "go1_set_state", "go1_get_state", "go1_enable_diag", "go1_get_diag",
     "go1_get_contacts", "go1_set_attr_f32", "go1_get_attr_f32", "go1_biped_info_host", "go1_biped_info_dev",
-    "go1_host_register", "go1_host_unregister",
+    "go1_host_register", "go1_host_unregister", "go1_stagger_phases",
 )
 
 
@@ -125,6 +125,7 @@ class Go1Lib:
         L.go1_host_register.argtypes = [vp, vp, C.c_size_t]
         L.go1_host_unregister.argtypes = [vp, vp]
         L.go1_biped_info_dev.argtypes = [vp, C.POINTER(C.c_void_p)]
+        L.go1_stagger_phases.argtypes = [vp]
         self.L = L
 
     def default_config(self) -> EnvConfig:
@@ -289,6 +290,10 @@ class Sim:
         self._check(self.lib.L.go1_get_contacts(self._h, int(env), buf, MAX_CONTACTS, C.byref(n)), "go1_get_contacts")
         return [dict(geom=b.geom, geom1=b.geom1, dim=b.dim, dist=b.dist, pos=np.array(b.pos[:]), force=np.array(b.force[:]))
                 for b in buf[: n.value]]
+
+    def stagger_phases(self):
+        """Throughput runs: spread the episode phases of a slab that was reset all at once (go1_stagger_phases)."""
+        self._check(self.lib.L.go1_stagger_phases(self._h), "go1_stagger_phases")
 
     def set_attr(self, name: str, value: float):
         self._check(self.lib.L.go1_set_attr_f32(self._h, name.encode(), float(value)), "go1_set_attr_f32")

@@ -21,7 +21,7 @@ def main():
     n = int(sys.argv[1]) if len(sys.argv) > 1 else 16384
     steps = int(sys.argv[2]) if len(sys.argv) > 2 else 60
     ctrl = sys.argv[3] if len(sys.argv) > 3 else "torque"
-    lib = Go1Lib()
+    lib = Go1Lib(os.environ["GO1_LIB"]) if os.environ.get("GO1_LIB") else Go1Lib()      # alternative build (tools/build_variant.sh)
     sim = Sim(load_model_blob(ctrl), n, lib=lib, seed=1234)
     lo, hi = sim.action_bounds()
     rng = np.random.default_rng(0)
@@ -40,8 +40,8 @@ def main():
         if t % 10 == 0 or t == steps - 1:
             it = info[:, 14]; nc = info[:, 15]
             q = np.percentile(it, [0, 50, 90, 99, 100])
-            # warp-level cost: 8 envs per warp execute max over the 8
-            wmax = it.reshape(-1, 8).max(axis=1)
+            # block-level cost: the 12 envs of a block run max-over-12 rounds (slab order here, the kernel's queue is work-sorted)
+            wmax = it.reshape(-1, 12).max(axis=1) if n % 12 == 0 else it[: n // 12 * 12].reshape(-1, 12).max(axis=1)
             print(f"step {t:4d} {dt*1e3:7.2f} ms | iters/ctrl-step min/med/p90/p99/max {q} mean {it.mean():.1f} warp-max mean {wmax.mean():.1f}"
                   f" | ncon med {np.median(nc):.0f} max {nc.max():.0f} mean {nc.mean():.2f} | healthy {info[:,13].mean():.3f} done {done.sum()}")
     if dump:

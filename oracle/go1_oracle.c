@@ -636,10 +636,11 @@ static void makeFrame(double *f) {
  * capsule-capsule and sphere-box restate MuJoCo's analytic functions [recalled].  MuJoCo 2.3.0 sends every
  * pair with a cylinder other than plane-cylinder through libccd's MPR (mjc_Convex, one contact, tolerance
  * 1e-6), which cannot be reproduced analytically: here those pairs use the exact closest-feature solution
- * that MPR approximates (point / segment vs solid cylinder, one contact).  capsule-box: closest point of
- * the segment to the box, then sphere-box there, plus the far end of the capsule when it is within the
- * margin as well (MuJoCo's mjc_CapsuleBox also returns up to two contacts, its second-contact rule is
- * restated in simplified form).  The CUDA kernel implements exactly the same rules (go1_pair.cuh). */
+ * that MPR approximates for sphere-cylinder, and for a capsule against a cylinder or a box the centre (box:
+ * for long patches both ends) of the CONTACT PATCH of the capsule axis (seg_patch): the closest point alone
+ * is ill-conditioned where a capsule lies along a face, the patch is not (MuJoCo's mjc_CapsuleBox also
+ * returns up to two contacts; its exact rules are not reproduced).  The CUDA kernel implements exactly the
+ * same rules (go1_pair.cuh). */
 static int sphereSphereRaw(const double *c1, double r1, const double *c2, double r2, const double *fall1, const double *fall2,
                            double margin, RawCon *con) {
     double dif[3] = {c2[0] - c1[0], c2[1] - c1[1], c2[2] - c1[2]};
@@ -750,52 +751,86 @@ static int sphereCylinderRaw(const double *c, double r, const double *p2, const 
     memcpy(con->frame, n, 24);
     return 1;
 }
-/* g(t) = d/dt of half the squared distance between the capsule-axis point pl + t*al (t in [-1, 1]) and a box / solid cylinder
- * given in ITS frame (cylinder: box == 0, sz = {R, R, h}), and g'(t).  g is continuous and non-decreasing. */
-static void seg_grad(const double *pl, const double *al, const double *sz, int box, double t, double *g, double *dg) {
+/* F(t) = squared distance between the capsule-axis point pl + t*al (t in [-1, 1]) and a box / solid cylinder given in ITS frame
+ * (cylinder: box == 0, sz = {R, R, h}), g(t) = F'(t) / 2 and g'(t).  F is convex along the line. */
+static void seg_eval(const double *pl, const double *al, const double *sz, int box, double t, double *F, double *g, double *dg) {
     double x[3] = {pl[0] + t * al[0], pl[1] + t * al[1], pl[2] + t * al[2]};
-    *g = 0; *dg = 0;
+    *F = 0; *g = 0; *dg = 0;
     if (box) {
         for (int i = 0; i < 3; i++) {
             double ex = x[i] - fmin(sz[i], fmax(-sz[i], x[i]));
-            *g += ex * al[i];
+            *F += ex * ex; *g += ex * al[i];
             if (ex != 0) *dg += al[i] * al[i];
         }
         return;
     }
     double ez = x[2] - fmin(sz[2], fmax(-sz[2], x[2]));
-    *g = ez * al[2];
+    *F = ez * ez; *g = ez * al[2];
     if (ez != 0) *dg = al[2] * al[2];
     double rho = sqrt(x[0] * x[0] + x[1] * x[1]);
     if (rho > sz[0]) {
         double u = (x[0] * al[0] + x[1] * al[1]) / rho, a2 = al[0] * al[0] + al[1] * al[1];
+        *F += (rho - sz[0]) * (rho - sz[0]);
         *g += (rho - sz[0]) * u;
         *dg += u * u + (rho - sz[0]) * (a2 - u * u) / rho;
     }
 }
-/* parameter of the capsule-axis point closest to the box / cylinder: root of the monotone g by Newton steps kept inside a
- * shrinking bracket (bisection when the step leaves it); the kernel runs the identical iteration (go1_pair.cuh) */
-static double seg_closest(const double *pl, const double *al, const double *sz, int box) {
-    double glo, ghi, dg;
-    seg_grad(pl, al, sz, box, -1.0, &glo, &dg);
-    if (glo >= 0) return -1.0;
-    seg_grad(pl, al, sz, box, 1.0, &ghi, &dg);
-    if (ghi <= 0) return 1.0;
-    double lo = -1.0, hi = 1.0, t = lo - glo * (hi - lo) / (ghi - glo);
-    for (int it = 0; it < 24; it++) {
-        double gt;
-        seg_grad(pl, al, sz, box, t, &gt, &dg);
-        if (gt == 0) break;
-        if (gt < 0) lo = t; else hi = t;
-        double tn = dg > 0 ? t - gt / dg : 0.5 * (lo + hi);
-        if (!(tn > lo && tn < hi)) tn = 0.5 * (lo + hi);
-        int done = fabs(tn - t) <= 1e-13;
-        t = tn;
-        if (done) break;
+/* Contact patch [t1, t2] of the capsule axis: the axis points within `reach` (radius + margin) of the body; 0 when there are none.
+ * First a point of minimum distance (root of the monotone g: Newton inside a shrinking bracket); along a face / the cylinder side it
+ * is not unique, it only serves as a point inside the patch.  The patch ends are roots of the convex F(t) = reach^2 approached by
+ * Newton from outside (monotone).  The kernel runs the identical steps (go1_pair.cuh seg_patch). */
+static int seg_patch(const double *pl, const double *al, const double *sz, int box, double reach, double *t1, double *t2) {
+    const double eps = 1e-13, r2 = reach * reach;
+    double Flo, Fhi, glo, ghi, dg, ts, Fs;
+    seg_eval(pl, al, sz, box, -1.0, &Flo, &glo, &dg);
+    seg_eval(pl, al, sz, box, 1.0, &Fhi, &ghi, &dg);
+    if (glo >= 0) { ts = -1; Fs = Flo; }
+    else if (ghi <= 0) { ts = 1; Fs = Fhi; }
+    else {
+        double lo = -1, hi = 1, gt;
+        ts = lo - glo * (hi - lo) / (ghi - glo);
+        for (int it = 0; it < 16; it++) {
+            seg_eval(pl, al, sz, box, ts, &Fs, &gt, &dg);
+            if (gt == 0) break;
+            if (gt < 0) lo = ts; else hi = ts;
+            double tn = dg > 0 ? ts - gt / dg : 0.5 * (lo + hi);
+            if (!(tn > lo && tn < hi)) tn = 0.5 * (lo + hi);
+            int done = fabs(tn - ts) <= eps;
+            ts = tn;
+            if (done) break;
+        }
+        seg_eval(pl, al, sz, box, ts, &Fs, &gt, &dg);
     }
-    return t;
+    if (Fs > r2) return 0;
+    *t1 = -1; *t2 = 1;
+    if (Flo > r2) {
+        double t = -1, F = Flo, g = glo;
+        for (int it = 0; it < 12 && F > r2 && g < 0; it++) {
+            double tn = t - 0.5 * (F - r2) / g;
+            if (tn > ts) tn = ts;
+            int done = fabs(tn - t) <= eps;
+            t = tn;
+            if (done) break;
+            seg_eval(pl, al, sz, box, t, &F, &g, &dg);
+        }
+        *t1 = t;
+    }
+    if (Fhi > r2) {
+        double t = 1, F = Fhi, g = ghi;
+        for (int it = 0; it < 12 && F > r2 && g > 0; it++) {
+            double tn = t - 0.5 * (F - r2) / g;
+            if (tn < ts) tn = ts;
+            int done = fabs(tn - t) <= eps;
+            t = tn;
+            if (done) break;
+            seg_eval(pl, al, sz, box, t, &F, &g, &dg);
+        }
+        *t2 = t;
+    }
+    return 1;
 }
-/* capsule (geom1) vs box or cylinder (geom2) */
+/* capsule (geom1) vs box or cylinder (geom2): sphere-vs-body contacts at the centre of the contact patch; a patch longer than half
+ * the capsule against a BOX gives two contacts at its ends (mjc_CapsuleBox also returns up to two), a cylinder pair one (as MPR) */
 static int capsuleConvex(const double *p1, const double *m1, const double *s1, const double *p2, const double *m2, const double *s2,
                          int box, double margin, RawCon *con) {
     double ax[3] = {m1[2], m1[5], m1[8]}, t[3] = {p1[0] - p2[0], p1[1] - p2[1], p1[2] - p2[2]}, pl[3], al[3];
@@ -809,14 +844,13 @@ static int capsuleConvex(const double *p1, const double *m1, const double *s1, c
         double lim = sz[i] + s1[0] + margin, a = pl[i] - al[i], b = pl[i] + al[i];
         if ((a > lim && b > lim) || (a < -lim && b < -lim)) return 0;
     }
-    double ts = seg_closest(pl, al, sz, box);
-    int n = 0;
-    for (int e = 0; e < 2; e++) {
-        double tt = e == 0 ? ts : (ts >= 0 ? -1.0 : 1.0);
-        if (e == 1 && !box) break;            /* cylinder pairs: one contact (as MPR) */
+    double t1, t2;
+    if (!seg_patch(pl, al, sz, box, s1[0] + margin, &t1, &t2)) return 0;
+    int two = box && (t2 - t1 > 1.0), n = 0;
+    for (int e = 0; e < (two ? 2 : 1); e++) {
+        double tt = two ? (e == 0 ? t1 : t2) : 0.5 * (t1 + t2);
         double c[3] = {p1[0] + ax[0] * s1[1] * tt, p1[1] + ax[1] * s1[1] * tt, p1[2] + ax[2] * s1[1] * tt};
         n += box ? sphereBoxRaw(c, s1[0], p2, m2, s2, margin, con + n) : sphereCylinderRaw(c, s1[0], p2, m2, s2, margin, con + n);
-        if (e == 0 && n == 0) break;
     }
     return n;
 }

@@ -3,8 +3,8 @@
 //
 // One lane = one geom pair.  Same rules as the fp64 oracle (oracle/go1_oracle.c "robot-robot narrowphase"):
 //   sphere-sphere, sphere-capsule, capsule-capsule, sphere-box      MuJoCo's analytic functions (engine_collision_primitive.c / _box.c)
-//   sphere-cylinder, capsule-cylinder                                exact closest feature, one contact (MuJoCo 2.3.0: MPR, tolerance 1e-6)
-//   capsule-box                                                      closest point of the axis segment, then sphere-box; far end when in reach
+//   sphere-cylinder                                                  exact closest feature, one contact (MuJoCo 2.3.0: MPR, tolerance 1e-6)
+//   capsule-cylinder, capsule-box                                    centre (box: long patches both ends) of the contact patch of the capsule axis, see seg_patch
 // The normal points from geom1 to geom2, geom1 being the geom of the lower type (mj_collideGeoms' swap).
 #pragma once
 
@@ -52,7 +52,7 @@ GO1_DEV void pp_sphere_sphere(const T* c1, T r1, const T* c2, T r2, const T* fa,
     if (cd2 > md * md) return;
     const T len = N::sqrt_(cd2), dist = len - r1 - r2;
     T n[3];
-    if (len < N::MINVAL) { cross3(n, fa, fb); normalize3_(n); }
+    if (len < N::GEOM_EPS) { cross3(n, fa, fb); normalize3_(n); }      // coincident centres (axes that intersect): mjraw_SphereSphere's fallback
     else { const T inv = T(1) / len; n[0] = dif[0] * inv; n[1] = dif[1] * inv; n[2] = dif[2] * inv; }
     if (dist < inc) {
         const T pos[3] = {c1[0] + n[0] * (r1 + T(0.5) * dist), c1[1] + n[1] * (r1 + T(0.5) * dist), c1[2] + n[2] * (r1 + T(0.5) * dist)};
@@ -140,60 +140,99 @@ GO1_DEV void pp_sphere_cyl(const T* c, T r, const GeomW<T>& q, T margin, T inc, 
     if (cd < inc) stage2_emit(st, pos, n, cd);
 }
 
-// g(t) = d/dt of half the squared distance between pl + t*al and a box (half sizes sz) / solid cylinder (sz = R, R, h) given in
-// its own frame, and g'(t).  g is continuous and non-decreasing (the squared distance to a convex set is convex along a line).
-template <typename T> GO1_DEV void seg_grad(const T* pl, const T* al, const T* sz, bool box, T t, T& g, T& dg) {
+// F(t) = squared distance between the axis point pl + t*al and a box (half sizes sz) / solid cylinder (sz = R, R, h) given in its
+// own frame, g(t) = F'(t) / 2 and g'(t).  F is convex along the line, g continuous and non-decreasing.
+template <typename T> GO1_DEV void seg_eval(const T* pl, const T* al, const T* sz, bool box, T t, T& F, T& g, T& dg) {
     typedef Num<T> N;
     const T x[3] = {pl[0] + t * al[0], pl[1] + t * al[1], pl[2] + t * al[2]};
-    g = 0; dg = 0;
+    F = 0; g = 0; dg = 0;
     if (box) {
 #pragma unroll
         for (int i = 0; i < 3; i++) {
             const T ex = x[i] - N::min_(sz[i], N::max_(-sz[i], x[i]));
-            g += ex * al[i];
+            F += ex * ex; g += ex * al[i];
             if (ex != 0) dg += al[i] * al[i];
         }
         return;
     }
     const T ez = x[2] - N::min_(sz[2], N::max_(-sz[2], x[2]));
-    g = ez * al[2];
+    F = ez * ez; g = ez * al[2];
     if (ez != 0) dg = al[2] * al[2];
     const T rho = N::sqrt_(x[0] * x[0] + x[1] * x[1]);
     if (rho > sz[0]) {
         const T u = (x[0] * al[0] + x[1] * al[1]) / rho, a2 = al[0] * al[0] + al[1] * al[1];
+        F += (rho - sz[0]) * (rho - sz[0]);
         g += (rho - sz[0]) * u;
         dg += u * u + (rho - sz[0]) * (a2 - u * u) / rho;
     }
 }
 
-// parameter t in [-1, 1] of the capsule-axis point closest to the box / cylinder: root of the monotone g by Newton steps
-// kept inside a shrinking bracket (bisection when the step leaves it); the oracle runs the identical iteration
-template <typename T> GO1_DEV T seg_closest(const T* pl, const T* al, const T* sz, bool box) {
+// The part of the capsule axis within `reach` (radius + margin) of the box / cylinder: the contact patch [t1, t2] in axis
+// parameters (t in [-1, 1]); returns false when no axis point is that close.  A point of minimum distance is found first (root of
+// the monotone g by Newton steps inside a shrinking bracket, bisection when a step leaves it): where the axis runs along a face or
+// the cylinder side that point is not unique and rounding picks one -- it only serves as a point INSIDE the patch.  The patch
+// ends are roots of the convex F(t) = reach^2 approached by Newton from outside (monotone, no safeguard needed) and are well
+// conditioned in every configuration, so contacts placed at the patch centre / ends do not jump.  The oracle runs the same steps.
+template <typename T> GO1_DEV bool seg_patch(const T* pl, const T* al, const T* sz, bool box, T reach, T& t1, T& t2) {
     typedef Num<T> N;
-    T glo, ghi, dg;
-    seg_grad(pl, al, sz, box, T(-1), glo, dg);
-    if (glo >= 0) return T(-1);
-    seg_grad(pl, al, sz, box, T(1), ghi, dg);
-    if (ghi <= 0) return T(1);
-    T lo = -1, hi = 1;
-    T t = lo - glo * (hi - lo) / (ghi - glo);
     const T eps = sizeof(T) == 4 ? T(1e-6) : T(1e-13);
+    const T r2 = reach * reach;
+    T Flo, Fhi, glo, ghi, dg, ts, Fs;
+    seg_eval(pl, al, sz, box, T(-1), Flo, glo, dg);
+    seg_eval(pl, al, sz, box, T(1), Fhi, ghi, dg);
+    if (glo >= 0) { ts = -1; Fs = Flo; }
+    else if (ghi <= 0) { ts = 1; Fs = Fhi; }
+    else {
+        T lo = -1, hi = 1;
+        ts = lo - glo * (hi - lo) / (ghi - glo);
 #pragma unroll 1
-    for (int it = 0; it < 24; it++) {
+        for (int it = 0; it < 16; it++) {
+            T gt;
+            seg_eval(pl, al, sz, box, ts, Fs, gt, dg);
+            if (gt == 0) break;
+            if (gt < 0) lo = ts; else hi = ts;
+            T tn = dg > 0 ? ts - gt / dg : T(0.5) * (lo + hi);
+            if (!(tn > lo && tn < hi)) tn = T(0.5) * (lo + hi);
+            const bool done = N::abs_(tn - ts) <= eps;
+            ts = tn;
+            if (done) break;
+        }
         T gt;
-        seg_grad(pl, al, sz, box, t, gt, dg);
-        if (gt == 0) break;
-        if (gt < 0) lo = t; else hi = t;
-        T tn = dg > 0 ? t - gt / dg : T(0.5) * (lo + hi);
-        if (!(tn > lo && tn < hi)) tn = T(0.5) * (lo + hi);
-        const bool done = N::abs_(tn - t) <= eps;
-        t = tn;
-        if (done) break;
+        seg_eval(pl, al, sz, box, ts, Fs, gt, dg);
     }
-    return t;
+    if (Fs > r2) return false;
+    t1 = -1; t2 = 1;
+    if (Flo > r2) {
+        T t = -1, F = Flo, g = glo;
+#pragma unroll 1
+        for (int it = 0; it < 12 && F > r2 && g < 0; it++) {
+            T tn = t - T(0.5) * (F - r2) / g;
+            if (tn > ts) tn = ts;
+            const bool done = N::abs_(tn - t) <= eps;
+            t = tn;
+            if (done) break;
+            seg_eval(pl, al, sz, box, t, F, g, dg);
+        }
+        t1 = t;
+    }
+    if (Fhi > r2) {
+        T t = 1, F = Fhi, g = ghi;
+#pragma unroll 1
+        for (int it = 0; it < 12 && F > r2 && g > 0; it++) {
+            T tn = t - T(0.5) * (F - r2) / g;
+            if (tn < ts) tn = ts;
+            const bool done = N::abs_(tn - t) <= eps;
+            t = tn;
+            if (done) break;
+            seg_eval(pl, al, sz, box, t, F, g, dg);
+        }
+        t2 = t;
+    }
+    return true;
 }
 
-// capsule a (geom1) vs box / cylinder q (geom2)
+// capsule a (geom1) vs box / cylinder q (geom2): sphere-vs-body contacts at the centre of the contact patch; a patch longer than
+// half the capsule against a BOX gives two contacts at its ends (mjc_CapsuleBox also returns up to two; a cylinder pair has one, as MPR)
 template <typename T>
 GO1_DEV void pp_capsule_convex(const GeomW<T>& a, const GeomW<T>& q, bool box, T margin, T inc, Stage2<T>& st) {
     T y[3];
@@ -207,11 +246,13 @@ GO1_DEV void pp_capsule_convex(const GeomW<T>& a, const GeomW<T>& q, bool box, T
         const T lim = sz[i] + a.s[0] + margin, u = pl[i] - al[i], v = pl[i] + al[i];
         if ((u > lim && v > lim) || (u < -lim && v < -lim)) return;
     }
-    const T ts = seg_closest(pl, al, sz, box);
+    T t1, t2;
+    if (!seg_patch(pl, al, sz, box, a.s[0] + margin, t1, t2)) return;
+    const bool two = box && (t2 - t1 > T(1));
 #pragma unroll 1
     for (int e = 0; e < 2; e++) {
-        if (e == 1 && (!box || st.cnt == 0)) break;
-        const T tt = e == 0 ? ts : (ts >= 0 ? T(-1) : T(1));
+        if (e == 1 && !two) break;
+        const T tt = two ? (e == 0 ? t1 : t2) : T(0.5) * (t1 + t2);
         const T c[3] = {a.c[0] + a.z[0] * a.s[1] * tt, a.c[1] + a.z[1] * a.s[1] * tt, a.c[2] + a.z[2] * a.s[1] * tt};
         if (box) pp_sphere_box(c, a.s[0], q, margin, inc, st); else pp_sphere_cyl(c, a.s[0], q, margin, inc, st);
     }

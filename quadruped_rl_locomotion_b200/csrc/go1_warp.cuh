@@ -87,6 +87,7 @@ template <> struct Num<float> {
     static GO1_DEV float max_(float a, float b) { return fmaxf(a, b); }
     static GO1_DEV float min_(float a, float b) { return fminf(a, b); }
     static constexpr float MINVAL = 1e-15f;
+    static constexpr float GEOM_EPS = 1e-6f;      // below this distance between two centres the direction is rounding noise (fp32)
 };
 template <> struct Num<double> {
     static GO1_DEV double sqrt_(double x) { return sqrt(x); }
@@ -97,6 +98,7 @@ template <> struct Num<double> {
     static GO1_DEV double max_(double a, double b) { return fmax(a, b); }
     static GO1_DEV double min_(double a, double b) { return fmin(a, b); }
     static constexpr double MINVAL = 1e-15;
+    static constexpr double GEOM_EPS = 1e-15;     // mjMINVAL, as MuJoCo and the oracle
 };
 
 // butterfly: every lane gets the bit-identical sum
@@ -1530,7 +1532,6 @@ GO1_NOINL void substep_w(const DevModel<T>& m, const EnvCfg<T>& cfg, WEnv<T>& E,
         int nall = nfl;
 #if GO1_SELF_COLLISION
         {
-            constexpr int MAXHIT = 64;
             T* gc = &E.c_s[0][0];
             int* hits = reinterpret_cast<int*>(gc + 3 * GFLAT);
 #pragma unroll 1
@@ -1545,36 +1546,36 @@ GO1_NOINL void substep_w(const DevModel<T>& m, const EnvCfg<T>& cfg, WEnv<T>& E,
             const unsigned char* gpa = cfg.gp_tab;
             const unsigned char* gpb = cfg.gp_tab + NGP;
             const T pmargin = m.pair_margin;
-            int nhit = 0;
+            int nhit = 0, p0 = 0;
 #pragma unroll 1
-            for (int p0 = 0; p0 < m.ngp; p0 += 32) {
-                const int pi = p0 + lane;
-                bool hit = false;
-                if (pi < m.ngp) {
-                    const int a = gpa[pi], b = gpb[pi];
-                    const T d[3] = {gc[3 * a] - gc[3 * b], gc[3 * a + 1] - gc[3 * b + 1], gc[3 * a + 2] - gc[3 * b + 2]};
-                    const T bound = m.flat_rb[a] + m.flat_rb[b] + pmargin;
-                    hit = dot3(d, d) <= bound * bound;
-                }
-                const unsigned mask = __ballot_sync(FULL, hit);
-                if (hit) {
-                    const int k = nhit + __popc(mask & ((1u << lane) - 1u));
-                    if (k < MAXHIT) hits[k] = pi;
-                }
-                nhit += __popc(mask);
-            }
-            __syncwarp();
-            if (nhit > MAXHIT) { nover += nhit - MAXHIT; nhit = MAXHIT; }
+            for (;;) {
+                // fill: bounding-sphere test of the next table entries until a full pass of 32 candidates is waiting (hits[] holds < 64)
 #pragma unroll 1
-            for (int h0 = 0; h0 < nhit; h0 += 32) {
+                while (p0 < m.ngp && nhit < 32) {
+                    const int pi = p0 + lane;
+                    bool hit = false;
+                    if (pi < m.ngp) {
+                        const int a = gpa[pi], b = gpb[pi];
+                        const T d[3] = {gc[3 * a] - gc[3 * b], gc[3 * a + 1] - gc[3 * b + 1], gc[3 * a + 2] - gc[3 * b + 2]};
+                        const T bound = m.flat_rb[a] + m.flat_rb[b] + pmargin;
+                        hit = dot3(d, d) <= bound * bound;
+                    }
+                    const unsigned mask = __ballot_sync(FULL, hit);
+                    if (hit) hits[nhit + __popc(mask & ((1u << lane) - 1u))] = pi;
+                    nhit += __popc(mask);
+                    p0 += 32;
+                }
+                __syncwarp();
+                if (nhit == 0) break;
+                const int take = nhit < 32 ? nhit : 32;
                 Stage2<T> st;
                 st.cnt = 0;
 #pragma unroll
                 for (int k = 0; k < 3; k++) { st.p[0][k] = st.p[1][k] = st.n[0][k] = st.n[1][k] = 0; }
                 st.d[0] = st.d[1] = 0;
                 int meta = 0;
-                if (h0 + lane < nhit) {
-                    const int pi = hits[h0 + lane];
+                if (lane < take) {
+                    const int pi = hits[lane];
                     int g1 = gpa[pi], g2 = gpb[pi];             // flat indices; geom1 = the lower geom type (mj_collideGeoms)
                     if (m.flat[g1].type > m.flat[g2].type) { const int t_ = g1; g1 = g2; g2 = t_; }
                     GeomW<T> w1, w2;
@@ -1611,6 +1612,12 @@ GO1_NOINL void substep_w(const DevModel<T>& m, const EnvCfg<T>& cfg, WEnv<T>& E,
                     }
                 }
                 nall += total;
+                // the candidates that did not fit into this pass move to the front
+                const int rest = 32 + lane < nhit ? hits[32 + lane] : 0;
+                __syncwarp();
+                if (32 + lane < nhit) hits[lane] = rest;
+                nhit -= take;
+                __syncwarp();
             }
             const int cap = nfl + PW < CW ? nfl + PW : CW;
             if (nall > cap) { nover += nall - cap; nall = cap; }
@@ -1729,6 +1736,10 @@ GO1_NOINL void substep_w(const DevModel<T>& m, const EnvCfg<T>& cfg, WEnv<T>& E,
                 E.c_aref[j][c] = ar;
                 E.c_aref[3 + j][c] = -cl.B * dot3(F + 3 * j, cv);
             }
+#ifdef GO1_EMU_TRACE
+            std::printf("ROW c %d b2 %d b1p %d cls %d dim %d dist %.6g D0 %.6g imp %.6g dA %.6g aref %.6g %.6g %.6g r %.5f %.5f %.5f n %.5f %.5f %.5f\n", c, b, b1p, meta_cls(meta), cl.dim, (double)dist,
+                        (double)E.c_D0[c], (double)imp, (double)dA, (double)E.c_aref[0][c], (double)E.c_aref[1][c], (double)E.c_aref[2][c], (double)r[0], (double)r[1], (double)r[2], (double)F[0], (double)F[1], (double)F[2]);
+#endif
             if (capture) {
                 T* e = con_out + 1 + c * 12;
                 e[0] = (T)(meta >> 16); e[1] = (T)cl.dim; e[2] = dist;

@@ -141,14 +141,21 @@ def random_start(env, rng, kind):
 def record_substeps(env, actions):
     """nstep=1 stepping (same physics as nstep=10) to expose every substep state."""
     d = env.data
-    out = {k: [] for k in ("qpos", "qvel", "warm", "qacc", "ctrl", "ncon", "solver_iter")}
+    out = {k: [] for k in ("qpos", "qvel", "warm", "qacc", "ctrl", "ncon", "solver_iter", "cfrc_ext", "con_geom", "con_geom1", "con_dim", "con_force")}
     for a in actions:
         d.ctrl[:] = a
         for _ in range(env.frame_skip):
             out["qpos"].append(d.qpos.copy()); out["qvel"].append(d.qvel.copy()); out["warm"].append(d.qacc_warmstart.copy())
             out["ctrl"].append(np.array(a, dtype=np.float64))
             env.sim.step(1)
-            out["qacc"].append(d.qacc.copy()); out["ncon"].append(d.ncon); out["solver_iter"].append(d.solver_iter)
+            env.sim.rne_post_constraint()      # cfrc_ext of THIS mj_step (does not change the state)
+            cons = [c for c in d.contact if c.exclude == 0]
+            g = -np.ones(MAXC, np.int32); g1 = -np.ones(MAXC, np.int32); dim = np.zeros(MAXC, np.int32); frc = np.zeros((MAXC, 6))
+            for i, c in enumerate(cons[:MAXC]):
+                g[i] = c.geom2; g1[i] = c.geom1; dim[i] = c.dim; frc[i, :c.dim] = d.efc_force[c.efc_address:c.efc_address + c.dim]
+            out["qacc"].append(d.qacc.copy()); out["ncon"].append(len(cons)); out["solver_iter"].append(d.solver_iter)
+            out["cfrc_ext"].append(d.cfrc_ext.copy()); out["con_geom"].append(g); out["con_geom1"].append(g1); out["con_dim"].append(dim)
+            out["con_force"].append(frc)
     out["qpos_final"] = d.qpos.copy(); out["qvel_final"] = d.qvel.copy()
     return {k: np.array(v) for k, v in out.items()}
 

@@ -481,7 +481,26 @@ __global__ void __launch_bounds__(GO1_WARPS * 32, GO1_MINBLOCKS) k_step(const __
             if (lane < 12) E.last_act[lane] = act;    // :529
             if (lane == 0) {
                 P.rew[env] = (float)reward;
-                P.work[env] = out.iters_total + 2 * out.ncon;
+                // queue key of the next control step (k_order: heaviest first).  Environments with robot-robot contacts go to the front
+                // in one group: the pair phases of a Newton round (pair Hessian, coupled-leg factorisation) then run in blocks whose
+                // warps mostly all need them, and the other blocks never wait for them.
+                {
+                    int w = (out.iters_total + 2 * out.ncon) >> 1;
+                    w = w > 63 ? 63 : w;
+#ifndef GO1_NO_PAIR_SORT
+                    // level 0: floor contacts only; 1: robot-robot contacts inside one leg / with the trunk; 2: between two legs
+                    int lvl = 0;
+                    if (!out.bad)
+                        for (int c = E.nfl; c < E.ncon; c++) {
+                            const int mt = E.c_meta[c];
+                            const int b2 = meta_b2(mt), b1 = meta_b1p(mt) - 1;
+                            const bool cross = b1 >= 1 && b2 >= 1 && (b1 - 1) / 3 != (b2 - 1) / 3;
+                            lvl = cross ? 2 : (lvl > 1 ? lvl : 1);
+                        }
+                    w += 64 * lvl;
+#endif
+                    P.work[env] = w;
+                }
                 P.done[env] = done ? 1 : 0;
                 P.trunc[env] = (truncated && !terminated && !nonfinite) ? 1 : 0;
                 if (P.info) {

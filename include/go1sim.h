@@ -42,7 +42,7 @@ extern "C" {
 #define GO1_NQ 19
 #define GO1_NV 18
 #define GO1_NBODY 14
-#define GO1_INFO_DIM 16
+#define GO1_INFO_DIM 20
 #define GO1_BIPED_INFO_DIM 12
 #define GO1_MAX_CONTACTS 40        /* contacts kept per environment and substep (floor + robot-robot); more are dropped and counted */
 #define GO1_MAX_PAIR_CONTACTS 16   /* robot-robot contacts among them */
@@ -175,9 +175,11 @@ int go1_reset(go1_handle h, const uint8_t* mask_dev, float* obs_dev, void* strea
 
 /* one control step for all envs, device buffers; asynchronous on `stream`.
  * obs_dev[N][48] f32 (reset obs for done envs), rew_dev[N] f32, done_dev[N] u8, trunc_dev[N] u8
- * (TimeLimit.truncated), terminal_obs_dev[N][48] (rows valid where done), info_dev[N][16] (nullable):
- * x, y, 8 reward_info terms (go1_mujoco_env.py:860-867,908-909), episode return, episode length,
- * health reason code, healthy flag, 2 spare. */
+ * (TimeLimit.truncated), terminal_obs_dev[N][48] (rows valid where done), info_dev[N][GO1_INFO_DIM] (nullable):
+ * [0] x, [1] y, [2..9] 8 reward_info terms (go1_mujoco_env.py:860-867,908-909), [10] episode return, [11] episode length,
+ * [12] health reason code (0 healthy, 1 not finite, 2 z, 3 roll, 4 pitch), [13] healthy flag, [14] Newton iterations of the
+ * control step, [15] active contacts, [16] the offending value of termination_details (:444-459), [17] robot-robot contacts,
+ * [18] contacts dropped for lack of slots, [19] spare. */
 int go1_step(go1_handle h, const float* actions_dev, float* obs_dev, float* rew_dev, uint8_t* done_dev,
              uint8_t* trunc_dev, float* terminal_obs_dev, float* info_dev, void* stream);
 

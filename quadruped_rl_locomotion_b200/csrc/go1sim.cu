@@ -509,6 +509,9 @@ __global__ void __launch_bounds__(GO1_WARPS * 32, GO1_MINBLOCKS) k_step(const __
                     inf[5] = (float)rec_r; inf[6] = (float)gu_r; inf[7] = (float)(-unh_c); inf[8] = (float)(-orient_c); inf[9] = (float)(-djp_c);
                     inf[10] = (float)ep_ret; inf[11] = (float)ep_len; inf[12] = (float)reason; inf[13] = ok ? 1.f : 0.f;
                     inf[14] = (float)out.iters_total; inf[15] = (float)out.ncon;
+                    // the value _get_health_status reports in termination_details (:444-459), robot-robot contacts and dropped contacts
+                    inf[16] = reason == 2 ? (float)qz : (reason == 3 ? (float)qroll : (reason == 4 ? (float)qpitch : 0.f));
+                    inf[17] = out.bad ? 0.f : (float)(E.ncon - E.nfl); inf[18] = (float)out.overflow; inf[19] = 0.f;
                     if (cfg.biped) inf[8] = inf[9] = 0.f;      // the two terms biped mode drops from reward_info (:905-909)
                 }
                 if (cfg.biped) {

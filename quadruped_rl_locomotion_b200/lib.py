@@ -14,7 +14,7 @@ import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 
-OBS_DIM, ACT_DIM, NQ, NV, NBODY, INFO_DIM, MAX_CONTACTS = 48, 12, 19, 18, 14, 16, 40
+OBS_DIM, ACT_DIM, NQ, NV, NBODY, INFO_DIM, MAX_CONTACTS = 48, 12, 19, 18, 14, 20, 40
 BIPED_INFO_DIM = 12
 
 ACTION_RANDOM, ACTION_POLICY, ACTION_ZERO = 0, 1, 2

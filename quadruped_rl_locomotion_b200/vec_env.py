@@ -86,6 +86,51 @@ def load_model_blob(ctrl_type: str = "torque", model_dir: Optional[str] = None) 
         return f.read()
 
 
+class StepInfos(list):
+    """``infos`` of one ``step``: a list of N per-environment dicts with every key of ``Go1MujocoEnv.step``'s info
+    (go1_mujoco_env.py:500-521, 860-909) plus SB3's ``terminal_observation`` / ``TimeLimit.truncated`` / ``episode`` for
+    finished environments.  Building 16 384 dicts per step would cost more than the simulation, so a dict is built the
+    first time its index is read and then kept (mutations by wrappers stay visible, and stay inside this step's object).
+    The object owns copies of the step's info rows: it remains valid after later steps."""
+
+    def __init__(self, env: "Go1CudaVecEnv", dones: np.ndarray):
+        super().__init__([None] * env.num_envs)
+        self._env = env
+        self._rows = env._info.copy()
+        self._brows = env._binfo.copy() if env.biped else None
+        self._trunc = env._trunc.copy()
+        self._dones = dones
+        self._t = round(time.time() - env._t_start, 6)
+        self._tobs = {int(i): env._tobs[i].astype(np.float64) for i in np.flatnonzero(dones)}
+
+    def _build(self, i: int) -> dict:
+        env = self._env
+        done = bool(self._dones[i])
+        d = env._info_dict(i, self._rows[i], None if self._brows is None else self._brows[i], done, bool(self._trunc[i]))
+        if done:                                   # SB3 VecEnv / Monitor contract
+            d["terminal_observation"] = self._tobs[i]
+            d["TimeLimit.truncated"] = bool(self._trunc[i])
+            d["episode"] = {"r": float(self._rows[i, 10]), "l": int(self._rows[i, 11]), "t": self._t}
+        return d
+
+    def __getitem__(self, i):
+        if isinstance(i, slice):
+            return [self[j] for j in range(*i.indices(len(self)))]
+        v = list.__getitem__(self, i)
+        if v is None:
+            j = i if i >= 0 else i + len(self)
+            v = self._build(j)
+            list.__setitem__(self, j, v)
+        return v
+
+    def __iter__(self):
+        for i in range(len(self)):
+            yield self[i]
+
+    def copy(self):
+        return [self[i] for i in range(len(self))]
+
+
 class Go1CudaVecEnv(_SB3VecEnv):
     """N Go1 environments stepped by one CUDA kernel per control step."""
 
@@ -94,7 +139,7 @@ class Go1CudaVecEnv(_SB3VecEnv):
     def __init__(self, num_envs: int, ctrl_type: str = "torque", biped: bool = False, rand_power: float = 0.0, *,
                  device: int = 0, seed: int = 0, env_id_offset: int = 0, desired_velocity_min=(-0.5, 0.0, 0.0),
                  desired_velocity_max=(0.5, 0.0, 0.0), model_dir: Optional[str] = None, precision: str = "f32",
-                 library: Optional[_lib.Go1Lib] = None, full_info: bool = False):
+                 library: Optional[_lib.Go1Lib] = None, full_info: bool = True):
         self._lib = library or _lib.Go1Lib(precision=precision)
         blob = load_model_blob(ctrl_type, model_dir)
         self.model = Model.from_blob(blob)
@@ -129,7 +174,10 @@ class Go1CudaVecEnv(_SB3VecEnv):
             except _lib.Go1Error:      # e.g. locked-memory limit: the library then stages through its own pinned buffers
                 pass
         self._t_start = time.time()
-        self._empty_infos = [dict() for _ in range(n)]
+        self._obs_f64 = [np.zeros((n, _lib.OBS_DIM), np.float64), np.zeros((n, _lib.OBS_DIM), np.float64)]
+        self._obs_flip = 0
+        self._healthy_ranges = ((float(cfg.healthy_z[0]), float(cfg.healthy_z[1])), (float(cfg.healthy_roll[0]), float(cfg.healthy_roll[1])),
+                                (float(cfg.healthy_pitch[0]), float(cfg.healthy_pitch[1])))
         if _HAVE_SB3:
             super().__init__(n, observation_space, action_space)
         else:
@@ -139,10 +187,19 @@ class Go1CudaVecEnv(_SB3VecEnv):
             self.reset_infos = [{} for _ in range(n)]
 
     # ------------------------------------------------------------------ VecEnv API (SB3 2.3.0 base_vec_env.py)
+    def _obs64(self) -> np.ndarray:
+        """The float64 observation batch SB3's contract asks for (``observation_space.dtype``), written into one of two
+        preallocated arrays that alternate from step to step: no 6 MB allocation + page faults per step, and the array of the
+        previous step (SB3 keeps it as ``_last_obs`` until the rollout buffer has copied it) stays intact for one more step."""
+        self._obs_flip ^= 1
+        out = self._obs_f64[self._obs_flip]
+        np.copyto(out, self._obs)
+        return out
+
     def reset(self) -> np.ndarray:
         self.sim.reset_host(self._obs)
         self.reset_infos = [{} for _ in range(self.num_envs)]
-        return self._obs.astype(np.float64)
+        return self._obs64()
 
     def step_async(self, actions: np.ndarray) -> None:
         a = np.asarray(actions, dtype=np.float32)
@@ -154,50 +211,39 @@ class Go1CudaVecEnv(_SB3VecEnv):
     def step_wait(self):
         self.sim.step_host(self._actions, self._obs, self._rew, self._done, self._trunc, self._tobs, self._info)
         dones = self._done.astype(bool)
-        if self.biped and (self.full_info or dones.any()):
+        if self.biped:
             self.sim.biped_info_host(self._binfo)
-        infos = self._make_infos(dones)
-        return self._obs.astype(np.float64), self._rew.copy(), dones, infos
+        infos = StepInfos(self, dones)
+        return self._obs64(), self._rew.copy(), dones, infos
 
     def step(self, actions: np.ndarray):
         self.step_async(actions)
         return self.step_wait()
 
-    def _make_infos(self, dones: np.ndarray) -> List[dict]:
-        """Per-env info dicts.  Done envs always get the keys SB3 reads; the per-step reward terms of
-        go1_mujoco_env.py:500-517,860-909 are materialised for every env only with ``full_info=True``
-        (16k dict constructions per step would dominate the step time otherwise)."""
-        if self.full_info:
-            infos = [self._info_dict(i) for i in range(self.num_envs)]
-        else:
-            infos = [dict() for _ in range(self.num_envs)] if dones.any() else self._empty_infos
-            if not dones.any():
-                return infos
-        now = time.time()
-        for i in np.flatnonzero(dones):
-            d = infos[i] if self.full_info else self._info_dict(i)
-            d["terminal_observation"] = self._tobs[i].astype(np.float64)
-            d["TimeLimit.truncated"] = bool(self._trunc[i])
-            d["episode"] = {"r": float(self._info[i, 10]), "l": int(self._info[i, 11]), "t": round(now - self._t_start, 6)}
-            infos[i] = d
-        return infos
-
-    def _info_dict(self, i: int) -> dict:
-        r = self._info[i]
+    def _info_dict(self, i: int, r: np.ndarray, b: Optional[np.ndarray], done: bool, trunc: bool) -> dict:
+        """The info dict of ``Go1MujocoEnv.step`` (go1_mujoco_env.py:500-521) for environment i from its info row."""
         d = {"x_position": float(r[0]), "y_position": float(r[1]), "distance_from_origin": float(np.hypot(r[0], r[1])),
-             "bipedal_success": False}
+             "termination_reason": "not_terminated", "termination_details": "No termination", "bipedal_success": False}
         healthy = r[13] > 0.5
-        reason = _REASONS.get(int(r[12]), "not_terminated")
-        if self._done[i] and not self._trunc[i]:
-            d["termination_reason"] = f"prolonged_{reason}"
-        elif not healthy:
-            d["termination_reason"] = "unhealthy_state_active"
+        code = int(r[12])
+        if code == 1:
+            details = "State values are not finite"                       # the reference prints the whole state vector here (:439)
+        elif code in (2, 3, 4):
+            name, unit, rng = {2: ("Z-position", "", self._healthy_ranges[0]), 3: ("Roll", " rad", self._healthy_ranges[1]),
+                               4: ("Pitch", " rad", self._healthy_ranges[2])}[code]
+            details = f"{name}: {float(r[16]):.3f}{unit}, Healthy Range: [{rng[0]:.2f}, {rng[1]:.2f}]{unit}"      # :444-459
         else:
-            d["termination_reason"] = "not_terminated"
+            details = "No termination"
+        reason = _REASONS.get(code, "not_terminated")
+        if done and not trunc:                                                                                       # :511-514
+            d["termination_reason"] = f"prolonged_{reason}"
+            d["termination_details"] = f"{details} (persisted for > {15.0:.2f}s)"
+        elif not healthy:                                                                                            # :515-518
+            d["termination_reason"] = "unhealthy_state_active"
+            d["termination_details"] = details
         for k, key in enumerate(INFO_KEYS[:6] if self.biped else INFO_KEYS):      # biped mode has no orientation / default-joint terms (:905-909)
             d[key] = float(r[2 + k])
         if self.biped:
-            b = self._binfo[i]
             for k, key in enumerate(BIPED_INFO_KEYS):
                 d[key] = float(b[k])
             d["bipedal_success"] = bool(b[10] > 0.5)                               # :520-521
@@ -218,6 +264,13 @@ class Go1CudaVecEnv(_SB3VecEnv):
         self._pinned = []
         self.sim.close()
 
+    def _shared(self, indices, what):
+        """All environments of the slab share one value of the simulator-level attributes (kernel parameters)."""
+        idx = self._indices(indices)
+        if sorted(set(idx)) != list(range(self.num_envs)):
+            raise ValueError(f"{what}: the attribute is shared by all {self.num_envs} environments of the slab; per-index values are "
+                             f"not supported (got indices={indices!r})")
+
     def get_attr(self, attr_name: str, indices=None) -> List[Any]:
         n = len(self._indices(indices))
         if attr_name in ("_rand_power", "rand_power"):
@@ -233,6 +286,8 @@ class Go1CudaVecEnv(_SB3VecEnv):
     def set_attr(self, attr_name: str, value: Any, indices=None) -> None:
         """``training_env.set_attr("_rand_power", v)`` (training_callback.py:64) really reaches the simulator
         (all envs share one value; per-index values are not supported)."""
+        if attr_name in ("_rand_power", "rand_power", "_desired_velocity_min", "_desired_velocity_max"):
+            self._shared(indices, f"set_attr({attr_name!r})")
         if attr_name in ("_rand_power", "rand_power"):
             self._rand_power = float(value)
             self.sim.set_attr("rand_power", float(value))
@@ -244,6 +299,16 @@ class Go1CudaVecEnv(_SB3VecEnv):
             setattr(self, attr_name, value)
 
     def env_method(self, method_name: str, *method_args, indices=None, **method_kwargs) -> List[Any]:
+        """There are no per-environment Python objects behind this VecEnv; the methods callers of the reference use through
+        ``env_method`` are answered here, anything else raises."""
+        idx = self._indices(indices)
+        if method_name in ("get_wrapper_attr", "__getattr__") and method_args:
+            return self.get_attr(method_args[0], indices)
+        if method_name == "set_wrapper_attr" and len(method_args) >= 2:
+            self.set_attr(method_args[0], method_args[1], indices)
+            return [None] * len(idx)
+        if method_name == "seed":
+            return list(self.seed(*method_args))[: len(idx)]
         raise NotImplementedError(f"env_method({method_name!r}): there are no per-env Python objects behind this VecEnv")
 
     def env_is_wrapped(self, wrapper_class, indices=None) -> List[bool]:
@@ -269,10 +334,19 @@ class Go1CudaVecEnv(_SB3VecEnv):
         return list(indices)
 
 
-def make_go1_vec_env(n_envs: int = 12, env_kwargs: Optional[dict] = None, seed: int = 0, **kw) -> Go1CudaVecEnv:
-    """Signature-compatible replacement for the call at reference ``train.py:44-50``:
-    ``make_vec_env(Go1MujocoEnv, env_kwargs=..., n_envs=..., seed=..., vec_env_cls=SubprocVecEnv)``."""
+def make_go1_vec_env(env_id=None, n_envs: int = 12, seed: int = 0, start_index: int = 0, monitor_dir=None, wrapper_class=None,
+                     env_kwargs: Optional[dict] = None, vec_env_cls=None, vec_env_kwargs: Optional[dict] = None,
+                     monitor_kwargs=None, wrapper_kwargs=None, **kw) -> Go1CudaVecEnv:
+    """Replacement for the call at reference ``train.py:44-50`` with SB3 ``make_vec_env``'s signature:
+    ``make_vec_env(Go1MujocoEnv, env_kwargs=..., n_envs=..., seed=..., vec_env_cls=SubprocVecEnv)``.  ``env_id`` (the env class),
+    ``vec_env_cls`` / ``vec_env_kwargs`` and the Monitor arguments are accepted and ignored: the slab IS the vectorised,
+    monitored environment (episode records come from the kernel).  ``wrapper_class`` is not supported (no per-env objects)."""
+    if wrapper_class is not None:
+        raise ValueError("make_go1_vec_env: wrapper_class is not supported (there are no per-env Python objects to wrap)")
+    if isinstance(env_id, int) and n_envs == 12:      # make_go1_vec_env(4096): the round-1 positional form
+        n_envs, env_id = env_id, None
     env_kwargs = dict(env_kwargs or {})
+    kw.setdefault("env_id_offset", int(start_index))
     env = Go1CudaVecEnv(n_envs, seed=seed, **env_kwargs, **kw)
     env.seed(seed)
     return env

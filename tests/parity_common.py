@@ -64,7 +64,7 @@ def run_teacher_forced(lib, ctrl: str, pre, post, idx, capture_contacts: bool = 
     actions = np.ascontiguousarray(post["action"][idx].astype(np.float32))
     obs = np.zeros((n, 48), np.float32); rew = np.zeros(n, np.float32)
     done = np.zeros(n, np.uint8); trunc = np.zeros(n, np.uint8)
-    tobs = np.zeros((n, 48), np.float32); info = np.zeros((n, 16), np.float32)
+    tobs = np.zeros((n, 48), np.float32); info = np.zeros((n, 20), np.float32)
     sim.step_host(actions, obs, rew, done, trunc, tobs, info)
     out = dict(obs=obs, rew=rew, done=done, trunc=trunc, tobs=tobs, info=info, state=[], diag=[], contacts=[])
     if biped:

@@ -155,7 +155,7 @@ def _run_env_logic(lib, ctrl, biped, n, seed, tol):
                       episode_return=0.0, bad_state=0)
     act = np.ascontiguousarray(np.array([s["action"] for s in states], np.float32))
     obs = np.zeros((n, 48), np.float32); rew = np.zeros(n, np.float32); done = np.zeros(n, np.uint8); trunc = np.zeros(n, np.uint8)
-    tobs = np.zeros((n, 48), np.float32); info = np.zeros((n, 16), np.float32)
+    tobs = np.zeros((n, 48), np.float32); info = np.zeros((n, 20), np.float32)
     sim.step_host(act, obs, rew, done, trunc, tobs, info)
     binfo = sim.biped_info_host() if biped else None
     logic = el.EnvLogic(model, biped=biped)

@@ -18,7 +18,7 @@ def _step_n(sim, n_steps, seed):
     rng = np.random.default_rng(seed)
     obs = np.zeros((n, 48), np.float32); rew = np.zeros(n, np.float32)
     done = np.zeros(n, np.uint8); trunc = np.zeros(n, np.uint8)
-    tobs = np.zeros((n, 48), np.float32); info = np.zeros((n, 16), np.float32)
+    tobs = np.zeros((n, 48), np.float32); info = np.zeros((n, 20), np.float32)
     hist = []
     for _ in range(n_steps):
         a = rng.uniform(lo, hi, size=(n, 12)).astype(np.float32)

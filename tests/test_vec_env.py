@@ -52,6 +52,7 @@ def _auto_reset(env, n):
     sim.set_state(2, qpos=q, unhealthy_steps=750)
     env.full_info = True
     obs, rew, dones, infos = env.step(np.zeros((n, 12), np.float32))
+    st1 = sim.get_state(1)          # state right after the auto-reset
     assert dones[1] and dones[2] and not dones[0]
     assert infos[1]["TimeLimit.truncated"] is True and infos[2]["TimeLimit.truncated"] is False
     for i in (1, 2):
@@ -61,13 +62,39 @@ def _auto_reset(env, n):
         assert np.all(obs[i, 0:6] == 0) and np.all(obs[i, 36:48] == 0)
         assert not np.array_equal(obs[i], infos[i]["terminal_observation"])
     assert infos[1]["episode"]["l"] == 6000 and infos[2]["termination_reason"] == "prolonged_unhealthy_z"
+    # termination_details (go1_mujoco_env.py:444-447, :513): the offending value and the healthy range, then the persistence note
+    z2 = float(infos[2]["termination_details"].split("Z-position: ")[1].split(",")[0])
+    assert infos[2]["termination_details"].endswith("Healthy Range: [0.22, 1.80] (persisted for > 15.00s)") and z2 < 0.22
+    assert infos[0]["termination_details"] in ("No termination",) or infos[0]["termination_reason"] == "unhealthy_state_active"
+    # every step hands out its OWN info objects: a wrapper that mutates them cannot leak into the next step or another env
+    infos[0]["leak"] = 1
+    _, _, _, infos_next = env.step(np.zeros((n, 12), np.float32))
+    assert "leak" not in infos_next[0] and infos[0]["leak"] == 1 and infos_next[0] is not infos[0]
+    assert len(infos_next) == n and isinstance(infos_next, list) and len(infos_next[:2]) == 2
+    # the float64 observation arrays alternate: the previous step's array is intact while the next step is returned
+    o1, _, _, _ = env.step(np.zeros((n, 12), np.float32)); keep = o1.copy()
+    o2, _, _, _ = env.step(np.zeros((n, 12), np.float32))
+    assert o1 is not o2 and np.array_equal(o1, keep) and o1.dtype == np.float64
+    with pytest.raises(ValueError):
+        env.set_attr("_rand_power", 0.5, indices=[0])          # one value per slab: per-index values are refused, not ignored
+    assert env.env_method("get_wrapper_attr", "_rand_power") == env.get_attr("_rand_power")
     assert "terminal_observation" not in infos[0]
     for k in ("x_position", "y_position", "distance_from_origin", "linear_vel_tracking_reward", "reward_ctrl",
               "reward_survive", "recovery_reward", "get_up_reward", "unhealthy_state_cost", "orientation_cost",
               "default_joint_position_cost", "termination_reason", "bipedal_success"):
         assert k in infos[0], k                                # go1_mujoco_env.py:500-517, 860-909
-    st = sim.get_state(1)
-    assert st["step"] == 0 and st["reset_count"] >= 1 and np.all(st["last_action"] == 0)
+    assert st1["step"] == 0 and st1["reset_count"] >= 1 and np.all(st1["last_action"] == 0)
+
+
+def test_make_go1_vec_env_signature(emu_lib_f32):
+    """``make_vec_env(Go1MujocoEnv, env_kwargs=..., n_envs=..., seed=..., vec_env_cls=SubprocVecEnv)`` (train.py:44-50) with the
+    env class positional and SB3's keyword set."""
+    from quadruped_rl_locomotion_b200.vec_env import make_go1_vec_env
+    env = make_go1_vec_env(object, env_kwargs={"ctrl_type": "position"}, n_envs=3, seed=5, vec_env_cls=object, library=emu_lib_f32)
+    assert env.num_envs == 3 and env.ctrl_type == "position"
+    env.close()
+    with pytest.raises(ValueError):
+        make_go1_vec_env(object, n_envs=2, wrapper_class=object, library=emu_lib_f32)
 
 
 def test_contract_emu(emu_lib_f32):

@@ -27,7 +27,7 @@ def main():
     rng = np.random.default_rng(0)
     obs = np.zeros((n, 48), np.float32); rew = np.zeros(n, np.float32)
     done = np.zeros(n, np.uint8); trunc = np.zeros(n, np.uint8)
-    tobs = np.zeros((n, 48), np.float32); info = np.zeros((n, 16), np.float32)
+    tobs = np.zeros((n, 48), np.float32); info = np.zeros((n, 20), np.float32)
     dump = os.environ.get("GO1_ITER_DUMP")
     hist_it, hist_nc = [], []
     for t in range(steps):

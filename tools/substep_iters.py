@@ -26,7 +26,7 @@ def main():
     lo, hi = sim.action_bounds()
     rng = np.random.default_rng(0)
     obs = np.zeros((n, 48), np.float32); rew = np.zeros(n, np.float32); done = np.zeros(n, np.uint8); trunc = np.zeros(n, np.uint8)
-    tobs = np.zeros((n, 48), np.float32); info = np.zeros((n, 16), np.float32)
+    tobs = np.zeros((n, 48), np.float32); info = np.zeros((n, 20), np.float32)
     its, ncs = [], []
     for t in range(steps):
         a = rng.uniform(lo, hi, size=(n, 12)).astype(np.float32)

@@ -211,6 +211,23 @@ int go1_last_rollout_timing(go1_handle h, float* ms, int* launches);
  * The Philox stream is (seed, env_id_offset + row, launch counter); every call advances the counter. */
 int go1_policy_act(go1_handle h, const Go1Policy* policy, const float* obs_dev, float* act_dev, int n, void* stream);
 
+/* Critic of the SB3 MlpPolicy (train.py:122-128, net_arch pi=[64,64], vf=[64,64]): mlp_extractor.value_net + value_net.
+ * Row-major [out][in] weights (torch layout), device pointers. */
+typedef struct Go1Critic {
+    const float* w0; const float* b0;    /* [64][48], [64] */
+    const float* w1; const float* b1;    /* [64][64], [64] */
+    const float* w2; const float* b2;    /* [1][64], [1]   */
+} Go1Critic;
+
+/* ActorCriticPolicy.forward for n rows of observations on the tensor cores (one tcgen05 CTA per 128 rows, tf32 operands,
+ * fp32 accumulation in tensor memory): actions = clip(mu + exp(log_std) * eps) (deterministic mean when log_std == NULL),
+ * values[n] (critic may be NULL -> values untouched), log_probs[n] of the UNCLIPPED Gaussian sample as SB3 stores them in its
+ * RolloutBuffer (either output pointer may be NULL).  Same Philox stream as go1_policy_act. */
+/* fp32 scalar reference of the same forward (one thread per row, CUDA cores): what the tensor-core kernel is tested against */
+int go1_policy_act_scalar(go1_handle h, const Go1Policy* policy, const float* obs_dev, float* act_dev, int n, void* stream);
+int go1_policy_forward(go1_handle h, const Go1Policy* actor, const Go1Critic* critic, const float* obs_dev, float* act_dev,
+                       float* values_dev, float* log_probs_dev, int n, void* stream);
+
 /* Biped mode only (cfg.biped != 0; GO1_EUNSUPPORTED otherwise): the extra reward_info entries of the LAST control
  * step, out[N][GO1_BIPED_INFO_DIM] f32 HOST buffer (synchronous D2H): biped_upright_reward, biped_front_contact_cost,
  * biped_rear_feet_airborne_cost, biped_front_foot_height_cost, biped_crossed_legs_cost, biped_low_rear_hips_cost,

@@ -586,7 +586,12 @@ __global__ void k_stagger(int* __restrict__ sint, int n, int max_unhealthy, unsi
     if (si[I_STEP] < k) si[I_STEP] = k;
 }
 
+}  // namespace go1
+#include "go1_policy_tc.cuh"
+namespace go1 {
+
 // 48-64-64-12 tanh MLP + Gaussian sampling + clip: one thread per env (weights in shared memory).
+// Scalar reference of the tensor-core kernel (go1_policy_tc.cuh): used by the CPU emulation build and by go1_policy_act_scalar (tests).
 // Round-1 version on the FP32 pipe; the tensor-core (tcgen05) version is tracked in DESIGN.md "next".
 __global__ void __launch_bounds__(128) k_policy(const float* __restrict__ obs, float* __restrict__ act, int n, Go1Policy pol,
                                                  const float* lo, const float* hi, unsigned long long seed, unsigned long long counter,
@@ -947,6 +952,9 @@ int go1_reset_host(go1_handle h, const uint8_t* mask, float* obs) {
     return GO1_OK;
 }
 
+static int launch_policy(go1_handle h, const Go1Policy* policy, const Go1Critic* critic, const float* obs_dev, float* act_dev,
+                         float* values_dev, float* logp_dev, int n, cudaStream_t s);
+
 int go1_rollout(go1_handle h, int n_steps, int action_mode, const Go1Policy* policy, Go1Stats* out, void* stream) {
     if (!h || n_steps < 0) return GO1_EINVAL;
     if (action_mode == GO1_ACTION_POLICY && !policy) { h->err = "go1_rollout: policy mode needs a policy"; return GO1_EINVAL; }
@@ -960,13 +968,8 @@ int go1_rollout(go1_handle h, int n_steps, int action_mode, const Go1Policy* pol
         P.obs = h->d_obs; P.rew = h->d_rew; P.done = h->d_done; P.trunc = h->d_trunc; P.term_obs = nullptr; P.info = nullptr;
         P.stats = h->stats;
         if (action_mode == GO1_ACTION_POLICY) {
-#ifdef GO1_EMU
-            const int tb = 1;
-#else
-            const int tb = 128;
-#endif
-            const int grid = (h->n_envs + tb - 1) / tb;
-            GO1_LAUNCH(k_policy, grid, tb, 0, s, h->d_obs, h->d_act, h->n_envs, *policy, h->d_lo, h->d_hi, h->seed, h->launch_counter, h->env_offset);
+            int prc = launch_policy(h, policy, nullptr, h->d_obs, h->d_act, nullptr, nullptr, h->n_envs, s);
+            if (prc != GO1_OK) return prc;
             launches++;
             P.actions = h->d_act; P.action_mode = 0;
         } else {
@@ -1004,7 +1007,42 @@ int go1_stagger_phases(go1_handle h) {
     return GO1_OK;
 }
 
-int go1_policy_act(go1_handle h, const Go1Policy* policy, const float* obs_dev, float* act_dev, int n, void* stream) {
+// actor (+ critic) forward on n observation rows: tcgen05 kernel on the GPU, the scalar kernel in the CPU emulation build (tests only)
+static int launch_policy(go1_handle h, const Go1Policy* policy, const Go1Critic* critic, const float* obs_dev, float* act_dev,
+                         float* values_dev, float* logp_dev, int n, cudaStream_t s) {
+#ifdef GO1_EMU
+    (void)critic; (void)values_dev; (void)logp_dev;
+    GO1_LAUNCH(k_policy, n, 1, 0, s, obs_dev, act_dev, n, *policy, h->d_lo, h->d_hi, h->seed, h->launch_counter, h->env_offset);
+#else
+    static bool attr_set = false;
+    if (!attr_set) {
+        CK(cudaFuncSetAttribute(k_policy_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::SM_TOTAL));
+        attr_set = true;
+    }
+    PolicyTCParams P;
+    P.obs = obs_dev; P.act = act_dev; P.value = critic ? values_dev : nullptr; P.logp = logp_dev; P.n = n;
+    P.aw0 = policy->w0; P.ab0 = policy->b0; P.aw1 = policy->w1; P.ab1 = policy->b1; P.aw2 = policy->w2; P.ab2 = policy->b2; P.log_std = policy->log_std;
+    P.cw0 = critic ? critic->w0 : nullptr; P.cb0 = critic ? critic->b0 : nullptr; P.cw1 = critic ? critic->w1 : nullptr;
+    P.cb1 = critic ? critic->b1 : nullptr; P.cw2 = critic ? critic->w2 : nullptr; P.cb2 = critic ? critic->b2 : nullptr;
+    P.lo = h->d_lo; P.hi = h->d_hi; P.seed = h->seed; P.counter = h->launch_counter; P.env_offset = h->env_offset;
+    k_policy_tc<<<(n + 127) / 128, 128, tc::SM_TOTAL, s>>>(P);
+    CK(cudaGetLastError());
+#endif
+    return GO1_OK;
+}
+
+int go1_policy_forward(go1_handle h, const Go1Policy* actor, const Go1Critic* critic, const float* obs_dev, float* act_dev,
+                       float* values_dev, float* log_probs_dev, int n, void* stream) {
+    if (!h || !actor || !obs_dev || !act_dev || n < 0) return GO1_EINVAL;
+    CK(cudaSetDevice(h->device));
+    if (n == 0) return GO1_OK;
+    int rc = launch_policy(h, actor, critic, obs_dev, act_dev, values_dev, log_probs_dev, n, stream ? (cudaStream_t)stream : h->stream);
+    h->launch_counter++;
+    return rc;
+}
+
+// the round-1 scalar kernel, kept as the fp32 reference the tensor-core kernel is tested against on the GPU
+int go1_policy_act_scalar(go1_handle h, const Go1Policy* policy, const float* obs_dev, float* act_dev, int n, void* stream) {
     if (!h || !policy || !obs_dev || !act_dev || n < 0) return GO1_EINVAL;
     CK(cudaSetDevice(h->device));
     cudaStream_t s = stream ? (cudaStream_t)stream : h->stream;
@@ -1017,6 +1055,16 @@ int go1_policy_act(go1_handle h, const Go1Policy* policy, const float* obs_dev, 
     GO1_LAUNCH(k_policy, (n + tb - 1) / tb, tb, 0, s, obs_dev, act_dev, n, *policy, h->d_lo, h->d_hi, h->seed, h->launch_counter, h->env_offset);
     h->launch_counter++;
     return GO1_OK;
+}
+
+int go1_policy_act(go1_handle h, const Go1Policy* policy, const float* obs_dev, float* act_dev, int n, void* stream) {
+    if (!h || !policy || !obs_dev || !act_dev || n < 0) return GO1_EINVAL;
+    CK(cudaSetDevice(h->device));
+    cudaStream_t s = stream ? (cudaStream_t)stream : h->stream;
+    if (n == 0) return GO1_OK;
+    int rc = launch_policy(h, policy, nullptr, obs_dev, act_dev, nullptr, nullptr, n, s);
+    h->launch_counter++;
+    return rc;
 }
 
 int go1_last_rollout_timing(go1_handle h, float* ms, int* launches) {

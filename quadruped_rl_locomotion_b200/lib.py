@@ -71,12 +71,16 @@ class Policy(C.Structure):
     _fields_ = [(k, C.c_void_p) for k in ("w0", "b0", "w1", "b1", "w2", "b2", "log_std")]
 
 
+class Critic(C.Structure):
+    _fields_ = [(k, C.c_void_p) for k in ("w0", "b0", "w1", "b1", "w2", "b2")]
+
+
 EXPORTS = (
     "go1_default_config", "go1_precision_bits", "go1_version", "go1_create", "go1_destroy", "go1_last_error",
     "go1_num_envs", "go1_action_bounds", "go1_reset", "go1_step", "go1_step_host", "go1_reset_host", "go1_rollout", "go1_policy_act",
     "go1_last_rollout_timing", "go1_set_state", "go1_get_state", "go1_enable_diag", "go1_get_diag",
     "go1_get_contacts", "go1_set_attr_f32", "go1_get_attr_f32", "go1_biped_info_host", "go1_biped_info_dev",
-    "go1_host_register", "go1_host_unregister", "go1_stagger_phases",
+    "go1_host_register", "go1_host_unregister", "go1_stagger_phases", "go1_policy_forward", "go1_policy_act_scalar",
 )
 
 
@@ -126,6 +130,8 @@ class Go1Lib:
         L.go1_host_unregister.argtypes = [vp, vp]
         L.go1_biped_info_dev.argtypes = [vp, C.POINTER(C.c_void_p)]
         L.go1_stagger_phases.argtypes = [vp]
+        L.go1_policy_forward.argtypes = [vp, C.POINTER(Policy), C.POINTER(Critic), vp, vp, vp, vp, i32, vp]
+        L.go1_policy_act_scalar.argtypes = [vp, C.POINTER(Policy), vp, vp, i32, vp]
         self.L = L
 
     def default_config(self) -> EnvConfig:
@@ -221,6 +227,17 @@ class Sim:
         """Actor forward + sampling on device buffers (``go1_policy_act``)."""
         self._check(self.lib.L.go1_policy_act(self._h, C.byref(policy), _ptr(obs), _ptr(act),
                                               int(self.n_envs if n is None else n), stream), "go1_policy_act")
+
+    def policy_act_scalar(self, policy: Policy, obs, act, n: int | None = None, stream=None):
+        """The fp32 scalar reference kernel of the same forward (``go1_policy_act_scalar``)."""
+        self._check(self.lib.L.go1_policy_act_scalar(self._h, C.byref(policy), _ptr(obs), _ptr(act),
+                                                     int(self.n_envs if n is None else n), stream), "go1_policy_act_scalar")
+
+    def policy_forward(self, policy: Policy, critic, obs, act, values=None, log_probs=None, n: int | None = None, stream=None):
+        """ActorCriticPolicy.forward on the tensor cores (``go1_policy_forward``): actions, values, log-probs; device buffers."""
+        self._check(self.lib.L.go1_policy_forward(self._h, C.byref(policy), C.byref(critic) if critic is not None else None, _ptr(obs), _ptr(act),
+                                                  _ptr(values) if values is not None else None, _ptr(log_probs) if log_probs is not None else None,
+                                                  int(self.n_envs if n is None else n), stream), "go1_policy_forward")
 
     # -- state / diagnostics
     def set_state(self, env: int, **kw):

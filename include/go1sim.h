@@ -219,14 +219,15 @@ typedef struct Go1Critic {
     const float* w2; const float* b2;    /* [1][64], [1]   */
 } Go1Critic;
 
+/* fp32 scalar reference of the actor forward (one thread per row, CUDA cores): what the tensor-core kernel is tested against */
+int go1_policy_act_scalar(go1_handle h, const Go1Policy* policy, const float* obs_dev, float* act_dev, int n, void* stream);
+
 /* ActorCriticPolicy.forward for n rows of observations on the tensor cores (one tcgen05 CTA per 128 rows, tf32 operands,
  * fp32 accumulation in tensor memory): actions = clip(mu + exp(log_std) * eps) (deterministic mean when log_std == NULL),
  * values[n] (critic may be NULL -> values untouched), log_probs[n] of the UNCLIPPED Gaussian sample as SB3 stores them in its
- * RolloutBuffer (either output pointer may be NULL).  Same Philox stream as go1_policy_act. */
-/* fp32 scalar reference of the same forward (one thread per row, CUDA cores): what the tensor-core kernel is tested against */
-int go1_policy_act_scalar(go1_handle h, const Go1Policy* policy, const float* obs_dev, float* act_dev, int n, void* stream);
+ * RolloutBuffer, raw_act[n][12] = that unclipped sample (any of the three may be NULL).  Same Philox stream as go1_policy_act. */
 int go1_policy_forward(go1_handle h, const Go1Policy* actor, const Go1Critic* critic, const float* obs_dev, float* act_dev,
-                       float* values_dev, float* log_probs_dev, int n, void* stream);
+                       float* values_dev, float* log_probs_dev, float* raw_act_dev, int n, void* stream);
 
 /* Biped mode only (cfg.biped != 0; GO1_EUNSUPPORTED otherwise): the extra reward_info entries of the LAST control
  * step, out[N][GO1_BIPED_INFO_DIM] f32 HOST buffer (synchronous D2H): biped_upright_reward, biped_front_contact_cost,

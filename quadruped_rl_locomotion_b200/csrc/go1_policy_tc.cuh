@@ -23,6 +23,7 @@ struct PolicyTCParams {
     float* act;                  // [n][12]
     float* value;                // [n] or null
     float* logp;                 // [n] or null
+    float* raw_act;              // [n][12] or null: the sample BEFORE the clip (what SB3's RolloutBuffer stores)
     int n;
     const float *aw0, *ab0, *aw1, *ab1, *aw2, *ab2, *log_std;       // actor (log_std null: deterministic mean action)
     const float *cw0, *cb0, *cw1, *cb1, *cw2, *cb2;                  // critic (all null: value is not computed)
@@ -247,6 +248,7 @@ __global__ void __launch_bounds__(128, 1) k_policy_tc(const __grid_constant__ Po
                     a += expf(ls) * nz[q];
                     lp += -0.5f * nz[q] * nz[q] - ls - 0.91893853320467274178f;     // log N(a; mu, sigma), before the clip (SB3 DiagGaussianDistribution.log_prob)
                 }
+                if (P.raw_act) P.raw_act[(size_t)e * 12 + o + q] = a;
                 P.act[(size_t)e * 12 + o + q] = fminf(bias[320 + o + q], fmaxf(bias[304 + o + q], a));
             }
         }

@@ -953,7 +953,7 @@ int go1_reset_host(go1_handle h, const uint8_t* mask, float* obs) {
 }
 
 static int launch_policy(go1_handle h, const Go1Policy* policy, const Go1Critic* critic, const float* obs_dev, float* act_dev,
-                         float* values_dev, float* logp_dev, int n, cudaStream_t s);
+                         float* values_dev, float* logp_dev, float* raw_dev, int n, cudaStream_t s);
 
 int go1_rollout(go1_handle h, int n_steps, int action_mode, const Go1Policy* policy, Go1Stats* out, void* stream) {
     if (!h || n_steps < 0) return GO1_EINVAL;
@@ -968,7 +968,7 @@ int go1_rollout(go1_handle h, int n_steps, int action_mode, const Go1Policy* pol
         P.obs = h->d_obs; P.rew = h->d_rew; P.done = h->d_done; P.trunc = h->d_trunc; P.term_obs = nullptr; P.info = nullptr;
         P.stats = h->stats;
         if (action_mode == GO1_ACTION_POLICY) {
-            int prc = launch_policy(h, policy, nullptr, h->d_obs, h->d_act, nullptr, nullptr, h->n_envs, s);
+            int prc = launch_policy(h, policy, nullptr, h->d_obs, h->d_act, nullptr, nullptr, nullptr, h->n_envs, s);
             if (prc != GO1_OK) return prc;
             launches++;
             P.actions = h->d_act; P.action_mode = 0;
@@ -1009,9 +1009,9 @@ int go1_stagger_phases(go1_handle h) {
 
 // actor (+ critic) forward on n observation rows: tcgen05 kernel on the GPU, the scalar kernel in the CPU emulation build (tests only)
 static int launch_policy(go1_handle h, const Go1Policy* policy, const Go1Critic* critic, const float* obs_dev, float* act_dev,
-                         float* values_dev, float* logp_dev, int n, cudaStream_t s) {
+                         float* values_dev, float* logp_dev, float* raw_dev, int n, cudaStream_t s) {
 #ifdef GO1_EMU
-    (void)critic; (void)values_dev; (void)logp_dev;
+    (void)critic; (void)values_dev; (void)logp_dev; (void)raw_dev;
     GO1_LAUNCH(k_policy, n, 1, 0, s, obs_dev, act_dev, n, *policy, h->d_lo, h->d_hi, h->seed, h->launch_counter, h->env_offset);
 #else
     static bool attr_set = false;
@@ -1020,7 +1020,7 @@ static int launch_policy(go1_handle h, const Go1Policy* policy, const Go1Critic*
         attr_set = true;
     }
     PolicyTCParams P;
-    P.obs = obs_dev; P.act = act_dev; P.value = critic ? values_dev : nullptr; P.logp = logp_dev; P.n = n;
+    P.obs = obs_dev; P.act = act_dev; P.value = critic ? values_dev : nullptr; P.logp = logp_dev; P.raw_act = raw_dev; P.n = n;
     P.aw0 = policy->w0; P.ab0 = policy->b0; P.aw1 = policy->w1; P.ab1 = policy->b1; P.aw2 = policy->w2; P.ab2 = policy->b2; P.log_std = policy->log_std;
     P.cw0 = critic ? critic->w0 : nullptr; P.cb0 = critic ? critic->b0 : nullptr; P.cw1 = critic ? critic->w1 : nullptr;
     P.cb1 = critic ? critic->b1 : nullptr; P.cw2 = critic ? critic->w2 : nullptr; P.cb2 = critic ? critic->b2 : nullptr;
@@ -1032,11 +1032,14 @@ static int launch_policy(go1_handle h, const Go1Policy* policy, const Go1Critic*
 }
 
 int go1_policy_forward(go1_handle h, const Go1Policy* actor, const Go1Critic* critic, const float* obs_dev, float* act_dev,
-                       float* values_dev, float* log_probs_dev, int n, void* stream) {
+                       float* values_dev, float* log_probs_dev, float* raw_act_dev, int n, void* stream) {
     if (!h || !actor || !obs_dev || !act_dev || n < 0) return GO1_EINVAL;
     CK(cudaSetDevice(h->device));
     if (n == 0) return GO1_OK;
-    int rc = launch_policy(h, actor, critic, obs_dev, act_dev, values_dev, log_probs_dev, n, stream ? (cudaStream_t)stream : h->stream);
+#ifdef GO1_EMU
+    if (critic || values_dev || log_probs_dev || raw_act_dev) { h->err = "go1_policy_forward: values / log-probs / raw actions need the tensor-core kernel (not in the CPU emulation build)"; return GO1_EUNSUPPORTED; }
+#endif
+    int rc = launch_policy(h, actor, critic, obs_dev, act_dev, values_dev, log_probs_dev, raw_act_dev, n, stream ? (cudaStream_t)stream : h->stream);
     h->launch_counter++;
     return rc;
 }
@@ -1062,7 +1065,7 @@ int go1_policy_act(go1_handle h, const Go1Policy* policy, const float* obs_dev, 
     CK(cudaSetDevice(h->device));
     cudaStream_t s = stream ? (cudaStream_t)stream : h->stream;
     if (n == 0) return GO1_OK;
-    int rc = launch_policy(h, policy, nullptr, obs_dev, act_dev, nullptr, nullptr, n, s);
+    int rc = launch_policy(h, policy, nullptr, obs_dev, act_dev, nullptr, nullptr, nullptr, n, s);
     h->launch_counter++;
     return rc;
 }

@@ -130,7 +130,7 @@ class Go1Lib:
         L.go1_host_unregister.argtypes = [vp, vp]
         L.go1_biped_info_dev.argtypes = [vp, C.POINTER(C.c_void_p)]
         L.go1_stagger_phases.argtypes = [vp]
-        L.go1_policy_forward.argtypes = [vp, C.POINTER(Policy), C.POINTER(Critic), vp, vp, vp, vp, i32, vp]
+        L.go1_policy_forward.argtypes = [vp, C.POINTER(Policy), C.POINTER(Critic), vp, vp, vp, vp, vp, i32, vp]
         L.go1_policy_act_scalar.argtypes = [vp, C.POINTER(Policy), vp, vp, i32, vp]
         self.L = L
 
@@ -233,10 +233,11 @@ class Sim:
         self._check(self.lib.L.go1_policy_act_scalar(self._h, C.byref(policy), _ptr(obs), _ptr(act),
                                                      int(self.n_envs if n is None else n), stream), "go1_policy_act_scalar")
 
-    def policy_forward(self, policy: Policy, critic, obs, act, values=None, log_probs=None, n: int | None = None, stream=None):
+    def policy_forward(self, policy: Policy, critic, obs, act, values=None, log_probs=None, n: int | None = None, stream=None, raw_act=None):
         """ActorCriticPolicy.forward on the tensor cores (``go1_policy_forward``): actions, values, log-probs; device buffers."""
         self._check(self.lib.L.go1_policy_forward(self._h, C.byref(policy), C.byref(critic) if critic is not None else None, _ptr(obs), _ptr(act),
                                                   _ptr(values) if values is not None else None, _ptr(log_probs) if log_probs is not None else None,
+                                                  _ptr(raw_act) if raw_act is not None else None,
                                                   int(self.n_envs if n is None else n), stream), "go1_policy_forward")
 
     # -- state / diagnostics

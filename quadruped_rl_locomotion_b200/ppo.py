@@ -302,7 +302,7 @@ class DevicePPO:
             rec = dict(iteration=len(self.history) + 1, timesteps=self.num_timesteps, mean_step_reward=s[2] / s[3], episodes=int(s[1]),
                        mean_episode_return=(s[0] / s[1]) if s[1] > 0 else None, fps=(self.num_timesteps - start) / (time.time() - t0),
                        policy_loss=float(diag["policy_loss"]), value_loss=float(diag["value_loss"]), approx_kl=float(diag["approx_kl"]),
-                       clip_fraction=float(diag["clip_fraction"]), std=float(self.net.log_std.exp().mean()))
+                       clip_fraction=float(diag["clip_fraction"]), std=float(self.net.log_std.detach().exp().mean()))
             self.history.append(rec)
             if log and self.rank == 0:
                 print(rec, flush=True)

@@ -229,6 +229,20 @@ int go1_policy_act_scalar(go1_handle h, const Go1Policy* policy, const float* ob
 int go1_policy_forward(go1_handle h, const Go1Policy* actor, const Go1Critic* critic, const float* obs_dev, float* act_dev,
                        float* values_dev, float* log_probs_dev, float* raw_act_dev, int n, void* stream);
 
+/* render_mode="rgb_array" (train.py:53-61: camera_name="tracking", width=1024, height=768; frames consumed by
+ * VideoRecordingCallback, training_callback.py:686-738).  The reference renders with MuJoCo's OpenGL renderer, which is unavailable
+ * on this box; this entry ray-casts the model's collision primitives and the checker floor on the GPU (no graphics API) into
+ * rgb[n_img][height][width][3] u8 (HOST buffer when rgb_is_host != 0, else device).  Camera: mode trackcom (follows the robot's
+ * centre of mass with a fixed world orientation); cam == NULL = the reference's `tracking` camera (go1_torque.xml:84). */
+typedef struct Go1Camera {
+    float pos[3];        /* camera position in the trunk frame at the reference pose qpos0 ("0 -1 0.8") */
+    float xaxis[3];      /* xyaxes "1 0 0 0 1 1": image x and y directions in the world (orthonormalised here) */
+    float yaxis[3];
+    float fovy_deg;      /* MuJoCo default 45 */
+} Go1Camera;
+int go1_render(go1_handle h, const Go1Camera* cam, const int32_t* env_ids_host, int n_img, int width, int height, uint8_t* rgb,
+               int rgb_is_host);
+
 /* Biped mode only (cfg.biped != 0; GO1_EUNSUPPORTED otherwise): the extra reward_info entries of the LAST control
  * step, out[N][GO1_BIPED_INFO_DIM] f32 HOST buffer (synchronous D2H): biped_upright_reward, biped_front_contact_cost,
  * biped_rear_feet_airborne_cost, biped_front_foot_height_cost, biped_crossed_legs_cost, biped_low_rear_hips_cost,

@@ -11,7 +11,8 @@ import sys
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 SRC = os.path.join(HERE, "csrc", "go1sim.cu")
-DEPS = [SRC, os.path.join(HERE, "csrc", "go1_warp.cuh"), os.path.join(HERE, "csrc", "go1_pair.cuh"), os.path.join(HERE, "csrc", "go1_model.h"),
+DEPS = [SRC, os.path.join(HERE, "csrc", "go1_warp.cuh"), os.path.join(HERE, "csrc", "go1_pair.cuh"), os.path.join(HERE, "csrc", "go1_policy_tc.cuh"),
+        os.path.join(HERE, "csrc", "go1_render.cuh"), os.path.join(HERE, "csrc", "go1_model.h"),
         os.path.join(os.path.dirname(HERE), "include", "go1sim.h"), os.path.abspath(__file__)]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-Xcompiler", "-fPIC",
               "-shared", "--expt-relaxed-constexpr"]

@@ -588,6 +588,9 @@ __global__ void k_stagger(int* __restrict__ sint, int n, int max_unhealthy, unsi
 
 }  // namespace go1
 #include "go1_policy_tc.cuh"
+#ifndef GO1_EMU
+#include "go1_render.cuh"
+#endif
 namespace go1 {
 
 // 48-64-64-12 tanh MLP + Gaussian sampling + clip: one thread per env (weights in shared memory).
@@ -639,6 +642,8 @@ struct Go1Sim {
     EnvCfg<real> cfg;
     DevModel<double> hmodel;
     DevModel<real>* dmodel = nullptr;
+    DevModel<float>* dmodel_f32 = nullptr;      // renderer's view of the model (== dmodel in the fp32 build)
+    int* d_envids = nullptr; unsigned char* d_rgb = nullptr; size_t rgb_cap = 0; int envids_cap = 0;
     real* sreal = nullptr; int* sint = nullptr;
     real* diag = nullptr; int* diag_i = nullptr; real* diag_con = nullptr;
     real* bipk = nullptr; float* bip_info = nullptr; real* bip_ready = nullptr;      // biped mode only
@@ -805,6 +810,9 @@ int go1_destroy(go1_handle h) {
     void* dev[] = {h->order, h->work, h->queue, h->dmodel, h->sreal, h->sint, h->diag, h->diag_i, h->diag_con, h->bipk, h->bip_info, h->bip_ready, h->stats, h->d_act, h->d_obs, h->d_rew, h->d_tobs,
                    h->d_info, h->d_done, h->d_trunc, h->d_mask, h->d_lo, h->d_hi};
     for (void* p : dev) if (p) cudaFree(p);
+    if (h->dmodel_f32 && (void*)h->dmodel_f32 != (void*)h->dmodel) cudaFree(h->dmodel_f32);
+    if (h->d_envids) cudaFree(h->d_envids);
+    if (h->d_rgb) cudaFree(h->d_rgb);
     for (auto& r : h->pinned) cudaHostUnregister(r.first);
     h->pinned.clear();
     void* host[] = {h->h_act, h->h_obs, h->h_rew, h->h_tobs, h->h_info, h->h_done, h->h_trunc, h->h_mask};
@@ -1093,6 +1101,69 @@ static int copy_fields(go1_handle h, void* base, size_t elem, int nfields, int e
     const size_t N = (size_t)h->n_envs;
     CK(cudaMemcpy2D(host, elem, (char*)base + elem * env, elem * N, elem, nfields, cudaMemcpyDeviceToHost));
     return GO1_OK;
+}
+
+int go1_render(go1_handle h, const Go1Camera* cam, const int32_t* env_ids_host, int n_img, int width, int height, uint8_t* rgb,
+               int rgb_is_host) {
+    if (!h || !env_ids_host || !rgb || n_img <= 0 || width <= 0 || height <= 0) { if (h) h->err = "go1_render: bad argument"; return GO1_EINVAL; }
+    for (int i = 0; i < n_img; i++) if (env_ids_host[i] < 0 || env_ids_host[i] >= h->n_envs) { h->err = "go1_render: environment index out of range"; return GO1_EINVAL; }
+#ifdef GO1_EMU
+    h->err = "go1_render: not available in the CPU emulation build";
+    return GO1_EUNSUPPORTED;
+#else
+    CK(cudaSetDevice(h->device));
+    if (!h->dmodel_f32) {
+        if (sizeof(real) == 4) h->dmodel_f32 = reinterpret_cast<DevModel<float>*>(h->dmodel);
+        else {
+            DevModel<float>* hm = new DevModel<float>();
+            cast_dev_model(h->hmodel, *hm);
+            cudaError_t e = cudaMalloc(&h->dmodel_f32, sizeof(DevModel<float>));
+            if (e == cudaSuccess) e = cudaMemcpy(h->dmodel_f32, hm, sizeof(DevModel<float>), cudaMemcpyHostToDevice);
+            delete hm;
+            if (e != cudaSuccess) { h->err = std::string("go1_render: ") + cudaGetErrorString(e); return GO1_ECUDA; }
+        }
+    }
+    const size_t bytes = (size_t)n_img * width * height * 3;
+    if (n_img > h->envids_cap) { if (h->d_envids) cudaFree(h->d_envids); CK(cudaMalloc((void**)&h->d_envids, sizeof(int) * n_img)); h->envids_cap = n_img; }
+    if (rgb_is_host && bytes > h->rgb_cap) { if (h->d_rgb) cudaFree(h->d_rgb); CK(cudaMalloc((void**)&h->d_rgb, bytes)); h->rgb_cap = bytes; }
+    CK(cudaMemcpyAsync(h->d_envids, env_ids_host, sizeof(int) * n_img, cudaMemcpyHostToDevice, h->stream));
+    RenderParams P;
+    P.model = h->dmodel_f32; P.sreal = h->sreal; P.real_is_double = sizeof(real) == 8; P.s_stride = S_STRIDE; P.n_envs = h->n_envs;
+    P.env_ids = h->d_envids; P.n_img = n_img; P.width = width; P.height = height;
+    Go1Camera c;
+    if (cam) c = *cam;
+    else { const Go1Camera def = {{0.f, -1.f, 0.8f}, {1.f, 0.f, 0.f}, {0.f, 1.f, 1.f}, 45.f}; c = def; }      // go1_torque.xml:84
+    P.fovy_deg = c.fovy_deg;
+    // mju_makeFrame-like orthonormalisation of xyaxes; z = x cross y (the camera looks along -z)
+    double x[3] = {c.xaxis[0], c.xaxis[1], c.xaxis[2]}, y[3] = {c.yaxis[0], c.yaxis[1], c.yaxis[2]};
+    double nx = std::sqrt(x[0] * x[0] + x[1] * x[1] + x[2] * x[2]);
+    if (nx < 1e-12) { h->err = "go1_render: degenerate camera axes"; return GO1_EINVAL; }
+    for (int k = 0; k < 3; k++) x[k] /= nx;
+    double d = x[0] * y[0] + x[1] * y[1] + x[2] * y[2];
+    for (int k = 0; k < 3; k++) y[k] -= d * x[k];
+    double ny = std::sqrt(y[0] * y[0] + y[1] * y[1] + y[2] * y[2]);
+    if (ny < 1e-12) { h->err = "go1_render: degenerate camera axes"; return GO1_EINVAL; }
+    for (int k = 0; k < 3; k++) y[k] /= ny;
+    const double z[3] = {x[1] * y[2] - x[2] * y[1], x[2] * y[0] - x[0] * y[2], x[0] * y[1] - x[1] * y[0]};
+    // trackcom: offset to the subtree COM of the trunk at qpos0 (mjModel.cam_poscom0)
+    const DevModel<double>& M = h->hmodel;
+    double com0[3] = {0, 0, 0};
+    for (int k = 0; k < 3; k++) com0[k] = M.t_mass * M.t_ipos[k];
+    for (int leg = 0; leg < NLEG; leg++) {
+        double p[3] = {0, 0, 0};
+        for (int i = 0; i < 3; i++) {
+            for (int k = 0; k < 3; k++) { p[k] += M.body_pos[leg][i][k]; com0[k] += M.mass[leg][i] * (p[k] + M.ipos[leg][i][k]); }
+        }
+    }
+    for (int k = 0; k < 3; k++) { com0[k] /= M.total_mass; P.cam_off[k] = (float)(c.pos[k] - com0[k]); P.cam_x[k] = (float)x[k]; P.cam_y[k] = (float)y[k]; P.cam_z[k] = (float)z[k]; }
+    P.rgb = rgb_is_host ? h->d_rgb : rgb;
+    dim3 block(16, 16), grid((width + 15) / 16, (height + 15) / 16, n_img);
+    k_render<<<grid, block, 0, h->stream>>>(P);
+    CK(cudaGetLastError());
+    if (rgb_is_host) CK(cudaMemcpyAsync(rgb, h->d_rgb, bytes, cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    return GO1_OK;
+#endif
 }
 
 int go1_biped_info_host(go1_handle h, float* out) {

@@ -71,6 +71,11 @@ class Policy(C.Structure):
     _fields_ = [(k, C.c_void_p) for k in ("w0", "b0", "w1", "b1", "w2", "b2", "log_std")]
 
 
+class Camera(C.Structure):
+    """``Go1Camera``: a trackcom camera (position in the trunk frame at qpos0, xyaxes, vertical field of view)."""
+    _fields_ = [("pos", C.c_float * 3), ("xaxis", C.c_float * 3), ("yaxis", C.c_float * 3), ("fovy_deg", C.c_float)]
+
+
 class Critic(C.Structure):
     _fields_ = [(k, C.c_void_p) for k in ("w0", "b0", "w1", "b1", "w2", "b2")]
 
@@ -80,7 +85,7 @@ EXPORTS = (
     "go1_num_envs", "go1_action_bounds", "go1_reset", "go1_step", "go1_step_host", "go1_reset_host", "go1_rollout", "go1_policy_act",
     "go1_last_rollout_timing", "go1_set_state", "go1_get_state", "go1_enable_diag", "go1_get_diag",
     "go1_get_contacts", "go1_set_attr_f32", "go1_get_attr_f32", "go1_biped_info_host", "go1_biped_info_dev",
-    "go1_host_register", "go1_host_unregister", "go1_stagger_phases", "go1_policy_forward", "go1_policy_act_scalar",
+    "go1_host_register", "go1_host_unregister", "go1_stagger_phases", "go1_policy_forward", "go1_policy_act_scalar", "go1_render",
 )
 
 
@@ -130,6 +135,7 @@ class Go1Lib:
         L.go1_host_unregister.argtypes = [vp, vp]
         L.go1_biped_info_dev.argtypes = [vp, C.POINTER(C.c_void_p)]
         L.go1_stagger_phases.argtypes = [vp]
+        L.go1_render.argtypes = [vp, C.POINTER(Camera), C.POINTER(C.c_int32), i32, i32, i32, vp, i32]
         L.go1_policy_forward.argtypes = [vp, C.POINTER(Policy), C.POINTER(Critic), vp, vp, vp, vp, vp, i32, vp]
         L.go1_policy_act_scalar.argtypes = [vp, C.POINTER(Policy), vp, vp, i32, vp]
         self.L = L
@@ -308,6 +314,17 @@ class Sim:
         self._check(self.lib.L.go1_get_contacts(self._h, int(env), buf, MAX_CONTACTS, C.byref(n)), "go1_get_contacts")
         return [dict(geom=b.geom, geom1=b.geom1, dim=b.dim, dist=b.dist, pos=np.array(b.pos[:]), force=np.array(b.force[:]))
                 for b in buf[: n.value]]
+
+    def render(self, env_ids=(0,), width: int = 1024, height: int = 768, camera: "Camera | None" = None, out=None):
+        """RGB frames [n][height][width][3] uint8 of the listed environments from the tracking camera (``go1_render``: CUDA
+        ray-caster, no graphics API).  ``out``: numpy array (host) or torch CUDA tensor (device) to write into."""
+        ids = (C.c_int32 * len(env_ids))(*[int(e) for e in env_ids])
+        if out is None:
+            out = np.zeros((len(env_ids), int(height), int(width), 3), np.uint8)
+        host = isinstance(out, np.ndarray)
+        self._check(self.lib.L.go1_render(self._h, C.byref(camera) if camera is not None else None, ids, len(env_ids), int(width), int(height),
+                                          _ptr(out), 1 if host else 0), "go1_render")
+        return out
 
     def stagger_phases(self):
         """Throughput runs: spread the episode phases of a slab that was reset all at once (go1_stagger_phases)."""

@@ -134,12 +134,13 @@ class StepInfos(list):
 class Go1CudaVecEnv(_SB3VecEnv):
     """N Go1 environments stepped by one CUDA kernel per control step."""
 
-    metadata = {"render_modes": []}
+    metadata = {"render_modes": ["rgb_array"]}
 
     def __init__(self, num_envs: int, ctrl_type: str = "torque", biped: bool = False, rand_power: float = 0.0, *,
                  device: int = 0, seed: int = 0, env_id_offset: int = 0, desired_velocity_min=(-0.5, 0.0, 0.0),
                  desired_velocity_max=(0.5, 0.0, 0.0), model_dir: Optional[str] = None, precision: str = "f32",
-                 library: Optional[_lib.Go1Lib] = None, full_info: bool = True):
+                 library: Optional[_lib.Go1Lib] = None, full_info: bool = True, render_mode: Optional[str] = None,
+                 camera_name: str = "tracking", width: int = 1024, height: int = 768):
         self._lib = library or _lib.Go1Lib(precision=precision)
         blob = load_model_blob(ctrl_type, model_dir)
         self.model = Model.from_blob(blob)
@@ -155,7 +156,11 @@ class Go1CudaVecEnv(_SB3VecEnv):
         action_space = Box(low=lo, high=hi, dtype=np.float32)
         self.ctrl_type, self.biped, self._rand_power = ctrl_type, bool(biped), float(rand_power)
         self.full_info = bool(full_info)
-        self.render_mode = None
+        if render_mode not in (None, "rgb_array"):
+            raise ValueError(f"render_mode {render_mode!r}: only None and 'rgb_array' (headless CUDA ray-caster) are available on this box")
+        if camera_name != "tracking":
+            raise ValueError("only the model's `tracking` camera (go1_torque.xml:84) is implemented")
+        self.render_mode, self.render_width, self.render_height = render_mode, int(width), int(height)
         n = int(num_envs)
         self._actions = np.zeros((n, _lib.ACT_DIM), np.float32)
         self._obs = np.zeros((n, _lib.OBS_DIM), np.float32)
@@ -320,11 +325,22 @@ class Go1CudaVecEnv(_SB3VecEnv):
         self.action_space.seed(seed)
         return [seed] * self.num_envs
 
-    def get_images(self):
-        return [None] * self.num_envs
+    def get_images(self, max_envs: int = 16):
+        """SB3 ``VecEnv.get_images``: one frame per environment (the first ``max_envs``; the rest are None -- 16 384 frames of
+        1024 x 768 would be 38 GB).  None everywhere unless ``render_mode == "rgb_array"``."""
+        if self.render_mode != "rgb_array":
+            return [None] * self.num_envs
+        k = min(self.num_envs, int(max_envs))
+        frames = self.sim.render(range(k), self.render_width, self.render_height)
+        return [frames[i] for i in range(k)] + [None] * (self.num_envs - k)
 
     def render(self, mode: Optional[str] = None):
-        return None  # graphics: unavailable on this box
+        """``Go1MujocoEnv(render_mode="rgb_array", camera_name="tracking", width=1024, height=768).render()`` (train.py:53-61,
+        training_callback.py:711) for environment 0: an [height, width, 3] uint8 frame from the CUDA ray-caster (the reference's
+        OpenGL renderer is unavailable on this box).  None when the env was not created with ``render_mode="rgb_array"``."""
+        if (mode or self.render_mode) != "rgb_array":
+            return None
+        return self.sim.render((0,), self.render_width, self.render_height)[0]
 
     def _indices(self, indices):
         if indices is None:

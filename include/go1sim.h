@@ -61,7 +61,8 @@ enum {
 typedef struct Go1EnvConfig {
     int32_t biped;                 /* go1_mujoco_env.py:41,:43: 1 = bipedal mode (reset pose :967-972, terms :869-904) */
     int32_t frame_skip;            /* :49  -> 10 */
-    int32_t max_episode_steps;     /* :64,:498 -> 6000 */
+    int32_t max_episode_steps;     /* :64,:498 -> 6000 = 120 s / dt.  Both limits are STEP COUNTS for dt = 10 x 0.002 s; a caller that
+                                    * changes frame_skip rescales them (the air-time bookkeeping :656 uses the model's dt itself) */
     int32_t max_unhealthy_steps;   /* :130,:497 -> terminate at the 751st consecutive unhealthy step: 750 */
     float rand_power;              /* :44,:974 */
     float fallen_start_prob;       /* :953 -> 0.2 */

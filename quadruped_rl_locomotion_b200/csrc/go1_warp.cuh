@@ -45,12 +45,15 @@ constexpr int NDOF = 18;    // 0..5 trunk (3 lin world, 3 rot body frame), 6 + 3
 // coupled-leg factorisation, line-search trip counts) let them drift apart inside a round, and every drifted warp is its
 // own instruction-fetch stream (the kernel is bound by instruction delivery).  A block barrier at
 // each phase boundary regroups them.  Every warp of the block executes the same NUMBER of barriers per round / substep.
+#ifndef GO1_PB_MASK
+#define GO1_PB_MASK 31         // which phase barriers exist: 1 F1 (before the pair collision), 2 F2 (after it), 4 B1 (before the Hessian),
+#endif                         // 8 B2 (before the factorisation), 16 B3 (before the line search); timing experiments only
 #if GO1_LOCKSTEP && GO1_PHASE_BARRIERS
-#define GO1_PB() __syncthreads()
+#define GO1_PBX(bit) do { if (GO1_PB_MASK & (bit)) __syncthreads(); } while (0)
 #else
-#define GO1_PB() ((void)0)
+#define GO1_PBX(bit) ((void)0)
 #endif
-#define GO1_PB3() do { GO1_PB(); GO1_PB(); GO1_PB(); } while (0)
+#define GO1_PB3() do { GO1_PBX(4); GO1_PBX(8); GO1_PBX(16); } while (0)
 #ifndef GO1_WARM_EXTRAP
 #define GO1_WARM_EXTRAP 1     // fp32 build: warm start = 2 a(t-1) - a(t-2) inside a control step (see substep_w)
 #endif
@@ -747,6 +750,7 @@ struct EnvCfg {
     int frame_skip, max_episode_steps, max_unhealthy_steps, solver_iterations;
     T rand_power, fallen_prob, vdes_min[3], vdes_max[3], reward_w[6], cost_w[11];
     T healthy_z[2], healthy_roll[2], healthy_pitch[2], sigma, obs_clip, tolerance;
+    T dt;                      // control period = model timestep x frame_skip (MujocoEnv.dt; air-time bookkeeping, go1_mujoco_env.py:656)
     // bipedal mode (go1_mujoco_env.py:43, :91-101, :967-972); read only when biped != 0
     int biped;
     T biped_w[10], biped_reset_z, biped_reset_qw, biped_reset_qy, foot_site[2][3];
@@ -1476,6 +1480,7 @@ GO1_NOINL void substep_w(const DevModel<T>& m, const EnvCfg<T>& cfg, WEnv<T>& E,
         if (lane < 3) E.com[lane] = com[lane];
     }
     __syncwarp();
+    GO1_PBX(128);      // F0 (experiment)
     // ------------------------------------------------------------------ mj_collision (plane vs geoms), contacts in geom order
     {
         int base = 0;
@@ -1524,7 +1529,7 @@ GO1_NOINL void substep_w(const DevModel<T>& m, const EnvCfg<T>& cfg, WEnv<T>& E,
             while (lo < hi) { const int mid = (lo + hi) >> 1; if (meta_b2(E.c_meta[mid]) < lane) lo = mid + 1; else hi = mid; }
             E.bstart[lane] = lo;
         }
-        GO1_PB();      // F1
+        GO1_PBX(1);    // F1
         // ---- robot-robot pairs (go1_pair.cuh).  Candidate geom pairs come from a table in (body1, body2, geom1, geom2) order --
         // mj_collision's order: bodies that are parent and child, geoms of one body and hip-motor pairs are not in it.  Pass 1:
         // bounding-sphere test of every table entry, the hits are compacted (order kept).  Pass 2: one lane per hit runs the
@@ -1566,6 +1571,9 @@ GO1_NOINL void substep_w(const DevModel<T>& m, const EnvCfg<T>& cfg, WEnv<T>& E,
                     p0 += 32;
                 }
                 __syncwarp();
+#if GO1_SELF_COLLISION == 3
+                nhit = 0;          // timing experiment only: bounding-sphere scan without the narrowphase
+#endif
                 if (nhit == 0) break;
                 const int take = nhit < 32 ? nhit : 32;
                 Stage2<T> st;
@@ -1631,7 +1639,7 @@ GO1_NOINL void substep_w(const DevModel<T>& m, const EnvCfg<T>& cfg, WEnv<T>& E,
         __syncwarp();
     }
     ncon = E.ncon;
-    GO1_PB();          // F2
+    GO1_PBX(2);        // F2
     // ------------------------------------------------------------------ mj_crb -> block-arrow M (+ armature)
     composite10(E.crb, lane);
     composite21(m, E.Kc, E.crb, false, lane);          // (overwrites xmat / xpos: collision is done)
@@ -1749,7 +1757,8 @@ GO1_NOINL void substep_w(const DevModel<T>& m, const EnvCfg<T>& cfg, WEnv<T>& E,
         if (capture && lane == 0) con_out[0] = (T)ncon;
     }
     __syncwarp();
-    } else { GO1_PB(); GO1_PB(); }   // active
+        GO1_PBX(64);   // F3 (experiment)
+    } else { GO1_PBX(128); GO1_PBX(1); GO1_PBX(2); GO1_PBX(64); }   // active
     // ------------------------------------------------------------------ mj_fwdConstraint: warmstart + Newton
     T a = as_, Ma = qfs, qfc = 0, hdiag = 0, grad = 0, cost = 0, oldcost = 0;
     const T scale = T(1) / (m.meaninertia * T(18));
@@ -1781,12 +1790,13 @@ GO1_NOINL void substep_w(const DevModel<T>& m, const EnvCfg<T>& cfg, WEnv<T>& E,
 #else
         if (conv) break;
 #endif
-        if (conv) { GO1_PB3(); continue; }
+        if (conv) { GO1_PBX(32); GO1_PB3(); continue; }
         do {
         if (lane < NDOF) E.xv[lane] = a;
         __syncwarp();
         body_motion(E, E.xv, E.bv[0], lane);
         const T rows = evaluate_rows(m, E, lane, a, dr, qfc, hdiag, frc_out);
+        GO1_PBX(32);   // B0 (experiment)
         const T gauss = lane < NDOF ? (Ma - qfs) * (a - as_) : T(0);
         const T cnew = warp_sum(rows + T(0.5) * gauss);
         if (phase == 0) {           // cost at qacc_smooth; now try the warmstart
@@ -1845,7 +1855,7 @@ GO1_NOINL void substep_w(const DevModel<T>& m, const EnvCfg<T>& cfg, WEnv<T>& E,
         if (nstall >= 3) { conv = true; GO1_PB3(); break; }
 #endif
         // ---- Hessian H = M + J'DJ (+ cone blocks), block-arrow; search = -H^-1 grad
-        GO1_PB();      // B1
+        GO1_PBX(4);    // B1
         if (contact_stiffness(m, E, lane)) {
             composite21(m, E.Kc, E.crb, true, lane);
             assemble_arrow(m, E, E.Kc, E.H, lane);
@@ -1862,7 +1872,7 @@ GO1_NOINL void substep_w(const DevModel<T>& m, const EnvCfg<T>& cfg, WEnv<T>& E,
 #ifdef GO1_EMU_COUNT
         if (lane == 0) { __atomic_fetch_add(&g_emu_rounds[pmode & 3], 1, __ATOMIC_RELAXED); if (E.ncon > E.nfl) __atomic_fetch_add(&g_emu_rounds[3], 1, __ATOMIC_RELAXED); }
 #endif
-        GO1_PB();      // B2
+        GO1_PBX(8);    // B2
         T s;
         if ((pmode & 3) == 3) {
             dense_factor(E, m, E.H, lane);
@@ -1882,11 +1892,11 @@ GO1_NOINL void substep_w(const DevModel<T>& m, const EnvCfg<T>& cfg, WEnv<T>& E,
         if ((GO1_DEC_EXIT && sizeof(T) == 4 && (iter > 0 || GO1_DEC_EXIT > 1)) || (iter > 0 && improvement < tol)) {
             const T dec = warp_sum(grad * s);
 #ifndef GO1_DBG_FIXED_ITERS
-            if (T(-0.5) * scale * dec < tol) { conv = true; GO1_PB(); break; }
+            if (T(-0.5) * scale * dec < tol) { conv = true; GO1_PBX(16); break; }
 #endif
         }
         // ---- exact line search (PrimalSearch)
-        GO1_PB();      // B3
+        GO1_PBX(16);   // B3
         if (lane < NDOF) E.xv[lane] = s;
         __syncwarp();
         const T Ms = arrow_matvec(E, E.M, lane);

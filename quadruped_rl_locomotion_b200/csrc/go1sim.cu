@@ -26,7 +26,9 @@
 #include "../../include/go1sim.h"
 #include "go1_warp.cuh"
 
+#ifndef GO1_VARIANT      // timing variants (tools/build_variant.sh) may shrink the capacities
 static_assert(go1::CW == GO1_MAX_CONTACTS && go1::PW == GO1_MAX_PAIR_CONTACTS, "include/go1sim.h capacities must match the kernel build");
+#endif
 
 #ifndef GO1_REAL
 #define GO1_REAL float
@@ -326,7 +328,7 @@ __global__ void __launch_bounds__(GO1_WARPS * 32, GO1_MINBLOCKS) k_step(const __
                 const int filt = curr | ((lastcon >> lane) & 1);
                 T air = E.air[lane];
                 const T first = (air > 0 && filt) ? T(1) : T(0);
-                air += T(0.02);
+                air += cfg.dt;
                 const T ts = air - T(0.2) > 0 ? air - T(0.2) : T(0);
                 air_l = ts * ts * first;
                 if (filt) air = 0;
@@ -700,6 +702,7 @@ const char* go1_last_error(go1_handle h) { return h ? h->err.c_str() : g_create_
 static void fill_cfg(EnvCfg<real>& k, const Go1EnvConfig& c, const DevModel<double>& M) {
     k.frame_skip = c.frame_skip; k.max_episode_steps = c.max_episode_steps; k.max_unhealthy_steps = c.max_unhealthy_steps;
     k.solver_iterations = c.solver_iterations > 0 ? c.solver_iterations : M.iterations;
+    k.dt = (real)(M.timestep * (double)c.frame_skip);
     k.rand_power = c.rand_power; k.fallen_prob = c.fallen_start_prob;
     for (int i = 0; i < 3; i++) { k.vdes_min[i] = c.desired_vel_min[i]; k.vdes_max[i] = c.desired_vel_max[i]; }
     // weights / ranges are the reference's fp64 literals: widen from the float config, but keep exact

@@ -13,7 +13,8 @@
  *                      (go1_mujoco_env.py:473-532: do_simulation = mj_step x frame_skip +
  *                      mj_rnePostConstraint, _get_obs :915-947, _calc_reward :791-913,
  *                      termination :487-498) + the worker's auto-reset / terminal_observation
- *   go1_step_host   <- the same call with HOST numpy buffers (what SB3 hands to VecEnv.step)
+ *   go1_step_host   <- the same call with HOST numpy buffers (what SB3 hands to VecEnv.step); go1_step_host_f64 returns
+ *                      the observations in the env's float64 observation dtype
  *   go1_rollout     <- test_max_envs.py:129-138 (random-action stepping loop, steps/s)
  *   go1_set_state / go1_get_state / go1_get_diag / go1_get_contacts
  *                   <- direct reads/writes of mjData the reference does
@@ -187,6 +188,11 @@ int go1_step(go1_handle h, const float* actions_dev, float* obs_dev, float* rew_
 /* same with HOST buffers: H2D of actions, kernel, D2H of results, synchronous (the VecEnv path). */
 int go1_step_host(go1_handle h, const float* actions, float* obs, float* rew, uint8_t* done, uint8_t* trunc,
                   float* terminal_obs, float* info);
+/* go1_step_host with the observation batch delivered as float64, obs64[N][48]: the dtype of the reference env's
+ * observation_space (gymnasium Box float64, go1_mujoco_env.py:151-153) that SB3's rollout buffer receives from VecEnv.step.  The
+ * widening runs on the device after the step kernel; every other buffer is as in go1_step_host. */
+int go1_step_host_f64(go1_handle h, const float* actions, double* obs64, float* rew, uint8_t* done, uint8_t* trunc,
+                      float* terminal_obs, float* info);
 int go1_reset_host(go1_handle h, const uint8_t* mask, float* obs);
 /* Optional: page-lock a caller-owned host buffer (cudaHostRegister).  go1_step_host copies to / from buffers that lie
  * inside a registered range directly (no staging through the library's own pinned buffers).  What SubprocVecEnv's

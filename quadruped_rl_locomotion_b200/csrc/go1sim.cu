@@ -588,6 +588,13 @@ __global__ void k_stagger(int* __restrict__ sint, int n, int max_unhealthy, unsi
     if (si[I_STEP] < k) si[I_STEP] = k;
 }
 
+// float32 -> float64 widening of the observation batch (go1_step_host_f64): SB3's observation dtype is float64
+// (gymnasium Box of the reference env), and 0.8 M conversions cost 0.5 ms on one host core but nothing here.
+__global__ void k_widen(const float* __restrict__ src, double* __restrict__ dst, int n) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) dst[i] = (double)src[i];
+}
+
 }  // namespace go1
 #include "go1_policy_tc.cuh"
 #ifndef GO1_EMU
@@ -657,6 +664,7 @@ struct Go1Sim {
     float *d_act = nullptr, *d_obs = nullptr, *d_rew = nullptr, *d_tobs = nullptr, *d_info = nullptr;
     uint8_t *d_done = nullptr, *d_trunc = nullptr, *d_mask = nullptr;
     float *h_act = nullptr, *h_obs = nullptr, *h_rew = nullptr, *h_tobs = nullptr, *h_info = nullptr;   // pinned staging
+    double *d_obs64 = nullptr, *h_obs64 = nullptr;      // go1_step_host_f64 only (allocated on first use)
     uint8_t *h_done = nullptr, *h_trunc = nullptr, *h_mask = nullptr;
     float *d_lo = nullptr, *d_hi = nullptr;
     cudaStream_t stream = nullptr;
@@ -816,6 +824,8 @@ int go1_destroy(go1_handle h) {
     if (h->dmodel_f32 && (void*)h->dmodel_f32 != (void*)h->dmodel) cudaFree(h->dmodel_f32);
     if (h->d_envids) cudaFree(h->d_envids);
     if (h->d_rgb) cudaFree(h->d_rgb);
+    if (h->d_obs64) cudaFree(h->d_obs64);
+    if (h->h_obs64) cudaFreeHost(h->h_obs64);
     for (auto& r : h->pinned) cudaHostUnregister(r.first);
     h->pinned.clear();
     void* host[] = {h->h_act, h->h_obs, h->h_rew, h->h_tobs, h->h_info, h->h_done, h->h_trunc, h->h_mask};
@@ -909,15 +919,24 @@ int go1_host_unregister(go1_handle h, void* ptr) {
     return GO1_EINVAL;
 }
 
-int go1_step_host(go1_handle h, const float* actions, float* obs, float* rew, uint8_t* done, uint8_t* trunc, float* terminal_obs, float* info) {
-    if (!h || !actions || !obs || !rew || !done || !trunc) { if (h) h->err = "go1_step_host: null buffer"; return GO1_EINVAL; }
+static int step_host_impl(go1_handle h, const float* actions, float* obs, double* obs64, float* rew, uint8_t* done, uint8_t* trunc, float* terminal_obs, float* info) {
+    if (!h || !actions || (!obs && !obs64) || !rew || !done || !trunc) { if (h) h->err = "go1_step_host: null buffer"; return GO1_EINVAL; }
     CK(cudaSetDevice(h->device));
     const size_t N = (size_t)h->n_envs;
     const size_t b_act = sizeof(float) * 12 * N, b_obs = sizeof(float) * 48 * N, b_rew = sizeof(float) * N, b_info = sizeof(float) * GO1_INFO_DIM * N;
     // pageable caller buffers are staged through the library's pinned ones; registered buffers are the DMA endpoints themselves
     const float* src_act = actions;
     if (!caller_pinned(h, actions, b_act)) { std::memcpy(h->h_act, actions, b_act); src_act = h->h_act; }
-    float* dst_obs = caller_pinned(h, obs, b_obs) ? obs : h->h_obs;
+    float* dst_obs = obs ? (caller_pinned(h, obs, b_obs) ? obs : h->h_obs) : nullptr;
+    double* dst_obs64 = nullptr;
+    if (obs64) {
+        if (!h->d_obs64) {
+            if (cudaMalloc((void**)&h->d_obs64, 2 * b_obs) != cudaSuccess || cudaMallocHost((void**)&h->h_obs64, 2 * b_obs) != cudaSuccess) {
+                h->err = "go1_step_host_f64: out of memory"; return GO1_ENOMEM;
+            }
+        }
+        dst_obs64 = caller_pinned(h, obs64, 2 * b_obs) ? obs64 : h->h_obs64;
+    }
     float* dst_rew = caller_pinned(h, rew, b_rew) ? rew : h->h_rew;
     uint8_t* dst_done = caller_pinned(h, done, N) ? done : h->h_done;
     uint8_t* dst_trunc = caller_pinned(h, trunc, N) ? trunc : h->h_trunc;
@@ -926,20 +945,41 @@ int go1_step_host(go1_handle h, const float* actions, float* obs, float* rew, ui
     CK(cudaMemcpyAsync(h->d_act, src_act, b_act, cudaMemcpyHostToDevice, h->stream));
     int rc = go1_step(h, h->d_act, h->d_obs, h->d_rew, h->d_done, h->d_trunc, h->d_tobs, info ? h->d_info : nullptr, h->stream);
     if (rc != GO1_OK) return rc;
-    CK(cudaMemcpyAsync(dst_obs, h->d_obs, b_obs, cudaMemcpyDeviceToHost, h->stream));
+    if (dst_obs) CK(cudaMemcpyAsync(dst_obs, h->d_obs, b_obs, cudaMemcpyDeviceToHost, h->stream));
+    if (dst_obs64) {
+        const int nel = (int)(48 * N);
+#ifdef GO1_EMU
+        GO1_LAUNCH(k_widen, nel, 1, 0, h->stream, h->d_obs, h->d_obs64, nel);
+#else
+        GO1_LAUNCH(k_widen, (nel + 255) / 256, 256, 0, h->stream, h->d_obs, h->d_obs64, nel);
+#endif
+        CK(cudaGetLastError());
+        CK(cudaMemcpyAsync(dst_obs64, h->d_obs64, 2 * b_obs, cudaMemcpyDeviceToHost, h->stream));
+    }
     CK(cudaMemcpyAsync(dst_rew, h->d_rew, b_rew, cudaMemcpyDeviceToHost, h->stream));
     CK(cudaMemcpyAsync(dst_done, h->d_done, N, cudaMemcpyDeviceToHost, h->stream));
     CK(cudaMemcpyAsync(dst_trunc, h->d_trunc, N, cudaMemcpyDeviceToHost, h->stream));
     if (dst_tobs) CK(cudaMemcpyAsync(dst_tobs, h->d_tobs, b_obs, cudaMemcpyDeviceToHost, h->stream));
     if (dst_info) CK(cudaMemcpyAsync(dst_info, h->d_info, b_info, cudaMemcpyDeviceToHost, h->stream));
     CK(cudaStreamSynchronize(h->stream));
-    if (dst_obs != obs) std::memcpy(obs, dst_obs, b_obs);
+    if (obs && dst_obs != obs) std::memcpy(obs, dst_obs, b_obs);
+    if (obs64 && dst_obs64 != obs64) std::memcpy(obs64, dst_obs64, 2 * b_obs);
     if (dst_rew != rew) std::memcpy(rew, dst_rew, b_rew);
     if (dst_done != done) std::memcpy(done, dst_done, N);
     if (dst_trunc != trunc) std::memcpy(trunc, dst_trunc, N);
     if (terminal_obs && dst_tobs != terminal_obs) std::memcpy(terminal_obs, dst_tobs, b_obs);
     if (info && dst_info != info) std::memcpy(info, dst_info, b_info);
     return GO1_OK;
+}
+
+int go1_step_host(go1_handle h, const float* actions, float* obs, float* rew, uint8_t* done, uint8_t* trunc, float* terminal_obs, float* info) {
+    if (!obs) { if (h) h->err = "go1_step_host: null buffer"; return GO1_EINVAL; }
+    return step_host_impl(h, actions, obs, nullptr, rew, done, trunc, terminal_obs, info);
+}
+
+int go1_step_host_f64(go1_handle h, const float* actions, double* obs64, float* rew, uint8_t* done, uint8_t* trunc, float* terminal_obs, float* info) {
+    if (!obs64) { if (h) h->err = "go1_step_host_f64: null buffer"; return GO1_EINVAL; }
+    return step_host_impl(h, actions, nullptr, obs64, rew, done, trunc, terminal_obs, info);
 }
 
 int go1_reset_host(go1_handle h, const uint8_t* mask, float* obs) {

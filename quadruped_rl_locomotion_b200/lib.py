@@ -82,7 +82,7 @@ class Critic(C.Structure):
 
 EXPORTS = (
     "go1_default_config", "go1_precision_bits", "go1_version", "go1_create", "go1_destroy", "go1_last_error",
-    "go1_num_envs", "go1_action_bounds", "go1_reset", "go1_step", "go1_step_host", "go1_reset_host", "go1_rollout", "go1_policy_act",
+    "go1_num_envs", "go1_action_bounds", "go1_reset", "go1_step", "go1_step_host", "go1_step_host_f64", "go1_reset_host", "go1_rollout", "go1_policy_act",
     "go1_last_rollout_timing", "go1_set_state", "go1_get_state", "go1_enable_diag", "go1_get_diag",
     "go1_get_contacts", "go1_set_attr_f32", "go1_get_attr_f32", "go1_biped_info_host", "go1_biped_info_dev",
     "go1_host_register", "go1_host_unregister", "go1_stagger_phases", "go1_policy_forward", "go1_policy_act_scalar", "go1_render",
@@ -119,6 +119,7 @@ class Go1Lib:
         L.go1_reset.argtypes = [vp, u8p, f32p, vp]
         L.go1_step.argtypes = [vp, f32p, f32p, f32p, u8p, u8p, f32p, f32p, vp]
         L.go1_step_host.argtypes = [vp, f32p, f32p, f32p, u8p, u8p, f32p, f32p]
+        L.go1_step_host_f64.argtypes = [vp, f32p, C.c_void_p, f32p, u8p, u8p, f32p, f32p]
         L.go1_reset_host.argtypes = [vp, u8p, f32p]
         L.go1_rollout.argtypes = [vp, i32, i32, C.POINTER(Policy), C.POINTER(Stats), vp]
         L.go1_policy_act.argtypes = [vp, C.POINTER(Policy), f32p, f32p, i32, vp]
@@ -215,6 +216,13 @@ class Sim:
         assert actions.dtype == np.float32 and actions.flags.c_contiguous and actions.shape == (self.n_envs, 12)
         self._check(self.lib.L.go1_step_host(self._h, _ptr(actions), _ptr(obs), _ptr(rew), _ptr(done), _ptr(trunc),
                                              _ptr(terminal_obs), _ptr(info)), "go1_step_host")
+
+    def step_host_f64(self, actions, obs64, rew, done, trunc, terminal_obs=None, info=None):
+        """``step_host`` with the observations delivered as float64 (widened on the device)."""
+        assert actions.dtype == np.float32 and actions.flags.c_contiguous and actions.shape == (self.n_envs, 12)
+        assert obs64.dtype == np.float64 and obs64.flags.c_contiguous and obs64.shape == (self.n_envs, 48)
+        self._check(self.lib.L.go1_step_host_f64(self._h, _ptr(actions), _ptr(obs64), _ptr(rew), _ptr(done), _ptr(trunc),
+                                                 _ptr(terminal_obs), _ptr(info)), "go1_step_host_f64")
 
     def reset_host(self, obs=None, mask=None):
         self._check(self.lib.L.go1_reset_host(self._h, _ptr(mask), _ptr(obs)), "go1_reset_host")

@@ -179,8 +179,16 @@ class Go1CudaVecEnv(_SB3VecEnv):
             except _lib.Go1Error:      # e.g. locked-memory limit: the library then stages through its own pinned buffers
                 pass
         self._t_start = time.time()
+        # float64 observation batches (observation_space.dtype): two arrays that alternate from step to step, written by the
+        # library itself (go1_step_host_f64 widens on the device): no 6 MB allocation, no host-side conversion pass per step
         self._obs_f64 = [np.zeros((n, _lib.OBS_DIM), np.float64), np.zeros((n, _lib.OBS_DIM), np.float64)]
         self._obs_flip = 0
+        for a in self._obs_f64:
+            try:
+                self.sim.host_register(a)
+                self._pinned.append(a)
+            except _lib.Go1Error:
+                pass
         self._healthy_ranges = ((float(cfg.healthy_z[0]), float(cfg.healthy_z[1])), (float(cfg.healthy_roll[0]), float(cfg.healthy_roll[1])),
                                 (float(cfg.healthy_pitch[0]), float(cfg.healthy_pitch[1])))
         if _HAVE_SB3:
@@ -192,19 +200,18 @@ class Go1CudaVecEnv(_SB3VecEnv):
             self.reset_infos = [{} for _ in range(n)]
 
     # ------------------------------------------------------------------ VecEnv API (SB3 2.3.0 base_vec_env.py)
-    def _obs64(self) -> np.ndarray:
-        """The float64 observation batch SB3's contract asks for (``observation_space.dtype``), written into one of two
-        preallocated arrays that alternate from step to step: no 6 MB allocation + page faults per step, and the array of the
-        previous step (SB3 keeps it as ``_last_obs`` until the rollout buffer has copied it) stays intact for one more step."""
+    def _next_obs64(self) -> np.ndarray:
+        """The array this step's float64 observations go to: the two preallocated batches alternate, so the array of the previous
+        step (SB3 keeps it as ``_last_obs`` until the rollout buffer has copied it) stays intact for one more step."""
         self._obs_flip ^= 1
-        out = self._obs_f64[self._obs_flip]
-        np.copyto(out, self._obs)
-        return out
+        return self._obs_f64[self._obs_flip]
 
     def reset(self) -> np.ndarray:
         self.sim.reset_host(self._obs)
         self.reset_infos = [{} for _ in range(self.num_envs)]
-        return self._obs64()
+        out = self._next_obs64()
+        np.copyto(out, self._obs)
+        return out
 
     def step_async(self, actions: np.ndarray) -> None:
         a = np.asarray(actions, dtype=np.float32)
@@ -214,12 +221,13 @@ class Go1CudaVecEnv(_SB3VecEnv):
         np.copyto(self._actions, a)
 
     def step_wait(self):
-        self.sim.step_host(self._actions, self._obs, self._rew, self._done, self._trunc, self._tobs, self._info)
+        obs = self._next_obs64()
+        self.sim.step_host_f64(self._actions, obs, self._rew, self._done, self._trunc, self._tobs, self._info)
         dones = self._done.astype(bool)
         if self.biped:
             self.sim.biped_info_host(self._binfo)
         infos = StepInfos(self, dones)
-        return self._obs64(), self._rew.copy(), dones, infos
+        return obs, self._rew.copy(), dones, infos
 
     def step(self, actions: np.ndarray):
         self.step_async(actions)

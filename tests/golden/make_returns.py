@@ -2,7 +2,10 @@
 position-control policies (``models/**/final_model.zip``) in the reference's own environment code
 (unmodified ``go1_mujoco_env.py``, imported from /root/reference) on the fp64 oracle physics.
 
-    python tests/golden/make_returns.py [n_episodes=1000] [n_procs=8] [max_steps=1500] [tag,tag,... = all]
+    python tests/golden/make_returns.py [n_episodes=1000] [n_procs=8] [max_steps=1500] [tag,tag,... = all] [first_seed=1000]
+
+With a first_seed other than 1000 the new episodes are APPENDED to the existing fixture (disjoint seeds), which is how the
+4000-episode files were extended to 12 000 for the policies whose first comparison sat near the 2 % bar.
 
 north_star's third correctness criterion: the CUDA simulator must reproduce the MEAN episode return of these
 policies within 2 % (trajectories are chaotic, so only the statistics are comparable).  Episodes are capped at
@@ -88,6 +91,7 @@ def main():
     procs = int(sys.argv[2]) if len(sys.argv) > 2 else 8
     max_steps = int(sys.argv[3]) if len(sys.argv) > 3 else 1500
     only = sys.argv[4].split(",") if len(sys.argv) > 4 else list(POLICIES)
+    seed0 = int(sys.argv[5]) if len(sys.argv) > 5 else 1000
     for tag, rel in POLICIES.items():
         if tag not in only or rel is None:
             continue
@@ -95,11 +99,16 @@ def main():
         assert pol["w0"].shape == (64, 48) and pol["w2"].shape == (12, 64)
         np.savez(os.path.join(OUT, f"policy_{tag}.npz"), **pol)
     for tag in only:
-        seeds = np.arange(n_ep) + 1000
+        seeds = np.arange(n_ep) + seed0
         chunks = [(tag, list(map(int, c)), max_steps) for c in np.array_split(seeds, procs * 4)]
         with mp.Pool(procs) as pool:
             res = [r for part in pool.map(_worker, chunks) for r in part]
         a = np.array(sorted(res))
+        path = os.path.join(OUT, f"returns_{tag}.npz")
+        if seed0 != 1000 and os.path.exists(path):
+            old = np.load(path)
+            assert int(old["max_steps"]) == max_steps and not set(old["seed"].astype(int)) & set(seeds.tolist())
+            a = np.concatenate([np.stack([old[k] for k in ("seed", "ret", "length", "fallen", "terminated", "x_final")], axis=1), a])
         np.savez(os.path.join(OUT, f"returns_{tag}.npz"), seed=a[:, 0], ret=a[:, 1], length=a[:, 2], fallen=a[:, 3],
                  terminated=a[:, 4], x_final=a[:, 5], max_steps=max_steps, v_des=np.array(V_DES), rand_power=RAND_POWER)
         print(f"{tag}: {len(a)} episodes, mean return {a[:, 1].mean():.3f} +- {a[:, 1].std() / np.sqrt(len(a)):.3f} (s.e.), "

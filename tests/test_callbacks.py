@@ -80,7 +80,7 @@ def test_evaluate_policy_on_the_vec_env(emu_lib_f32, tmp_path):
     env = Go1CudaVecEnv(4, ctrl_type="torque", library=emu_lib_f32, seed=2)
     env.sim.set_state(0, step=5995)                         # this environment hits the time limit during the evaluation
     predict = lambda obs, deterministic=True: (np.zeros((4, 12), np.float32), None)
-    env.reset = lambda: env._obs64()                         # keep the state edited above (reset would overwrite it)
+    env.reset = lambda: env._obs.astype(np.float64)                      # keep the state edited above (reset would overwrite it)
     res = cb.evaluate_policy(env, predict, max_steps=8)
     assert res["lengths"][0] == 5 and np.all(res["lengths"][1:] == 8) and len(res["failures"]) == 1
     h = cb.TrainingHistory(best_model_save_path=str(tmp_path))

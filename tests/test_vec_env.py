@@ -234,7 +234,7 @@ def _registered_vs_pageable(emu_lib_f32, n):
     range falls back to staging."""
     from quadruped_rl_locomotion_b200.lib import Sim
     env = Go1CudaVecEnv(n, library=emu_lib_f32, seed=4)
-    assert len(env._pinned) == 7
+    assert len(env._pinned) == 9          # actions, obs, terminal obs, reward, done, trunc, info + the two float64 observation batches
     sim2 = Sim(pc.model_blob("torque"), n, lib=emu_lib_f32, seed=4)
     env.reset(); sim2.reset_host()
     rng = np.random.default_rng(0)
@@ -244,6 +244,10 @@ def _registered_vs_pageable(emu_lib_f32, n):
         o1, r1, d1, _ = env.step(a)
         sim2.step_host(a, obs, rew, done, trunc)
         assert np.array_equal(o1.astype(np.float32), obs) and np.array_equal(r1, rew) and np.array_equal(d1, done.astype(bool))
+    # go1_step_host_f64 (the VecEnv's path, registered float64 arrays above) through a pageable float64 array: staged, same values
+    o64 = np.full((n, 48), np.nan)
+    env.sim.step_host_f64(a, o64, rew, done, trunc); sim2.step_host(a, obs, rew, done, trunc)
+    assert o64.dtype == np.float64 and np.array_equal(o64, obs.astype(np.float64))
     big = np.zeros((n + 1, 48), np.float32)
     env.sim.host_register(big)
     env.sim.step_host(a, big[1:], rew, done, trunc)          # inside the registered range, not at its start

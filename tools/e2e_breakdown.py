@@ -21,7 +21,8 @@ def main():
     rng = np.random.default_rng(0)
     lo, hi = env.action_space.low, env.action_space.high
     acts = [rng.uniform(lo, hi, (n, 12)).astype(np.float32) for _ in range(8)]
-    for i in range(100):
+    s.rollout(300, ACTION_RANDOM, None); s.stagger_phases(); s.rollout(100, ACTION_RANDOM, None)     # bench.py's burn-in: episodes end every step
+    for i in range(10):
         env.step(acts[i % 8])
     obs_pageable = np.zeros((n, 48), np.float32)
 

@@ -1,6 +1,9 @@
 """Profiling driver: W warm-up + K timed device-resident control steps of the fused step kernel.
 
-    python tools/prof_step.py [n_envs] [warmup] [steps] [ctrl] [actions]
+    python tools/prof_step.py [n_envs] [warmup] [steps] [ctrl] [stagger]
+
+With a fifth argument "stagger" the warm-up is bench.py's burn-in: `warmup` steps, go1_stagger_phases, 100 more steps (the
+steady-state mix of episode phases; k_step launches before the timed ones: warmup + 100).
 
 Prints ms per control step (CUDA events inside go1_rollout) and the rollout statistics.  Short enough to
 wrap in `ncu --set full -k regex:k_step -s <warmup+2> -c 1` (B200_PROFILING.md)."""
@@ -23,6 +26,10 @@ def main():
     sim = Sim(load_model_blob(ctrl), n, lib=Go1Lib(libpath) if libpath else Go1Lib(), seed=1234)
     for _ in range(warm):
         sim.rollout(1, ACTION_RANDOM, None)
+    if len(sys.argv) > 5 and sys.argv[5] == "stagger":
+        sim.stagger_phases()
+        for _ in range(100):
+            sim.rollout(1, ACTION_RANDOM, None)
     tot = 0.0
     for _ in range(steps):
         st = sim.rollout(1, ACTION_RANDOM, None)

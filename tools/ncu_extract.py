@@ -30,7 +30,9 @@ SELECT = re.compile(
     r"smsp__thread_inst_executed_per_inst_executed\.ratio|smsp__thread_inst_executed_pred_on_per_inst_executed\.ratio|"
     r"smsp__pcsamp_warps_issue_stalled_\w+|smsp__pcsamp_sample_buffer_full|smsp__pcsamp_interval\w*|"
     r"smsp__sass_thread_inst_executed_op_(fadd|fmul|ffma)_pred_on\.sum|sm__sass_inst_executed_op_(shared|local|global)_(ld|st)\.sum|"
-    r"smsp__inst_executed_op_(shared|local)_\w+\.sum|lts__t_sector_hit_rate\.pct|sm__throughput\.avg\.pct_of_peak_sustained_elapsed)$")
+    r"smsp__inst_executed_op_(shared|local)_\w+\.sum|lts__t_sector_hit_rate\.pct|sm__throughput\.avg\.pct_of_peak_sustained_elapsed|"
+    r"smsp__sass_thread_inst_executed_op_f(add|mul|fma)_pred_on\.sum\.per_cycle_elapsed|smsp__cycles_elapsed\.avg(\.per_second)?|"
+    r"smsp__sass_inst_executed_op_local_(ld|st)\.sum)$")
 
 
 def ncu(*args):
@@ -55,6 +57,10 @@ def main():
                   if n.startswith("smsp__pcsamp_warps_issue_stalled_") and not n.endswith("_not_issued"))
         bar = float(sel["smsp__pcsamp_warps_issue_stalled_barrier"][1].replace(",", ""))
         f.write(f"# derived: barrier share of the stall samples = {bar:.0f} / {tot:.0f} = {bar / tot:.3f}\n")
+        g = lambda k: float(sel[k][1].replace(",", ""))
+        flop = (g("smsp__sass_thread_inst_executed_op_fadd_pred_on.sum.per_cycle_elapsed") + g("smsp__sass_thread_inst_executed_op_fmul_pred_on.sum.per_cycle_elapsed")
+                + 2 * g("smsp__sass_thread_inst_executed_op_ffma_pred_on.sum.per_cycle_elapsed")) * g("smsp__cycles_elapsed.avg")
+        f.write(f"# derived: executed FP32 work (fadd + fmul + 2 ffma, predicated-on threads) = {flop:.4g} FLOP per launch = {flop / n_envs:.4g} per env-step\n")
 
     def to_bytes(name):
         u, v = sel[name]; v = float(v.replace(",", ""))

@@ -751,6 +751,67 @@ static int sphereCylinderRaw(const double *c, double r, const double *p2, const 
     memcpy(con->frame, n, 24);
     return 1;
 }
+/* Signed distance of the 2-D point (px, py) to the rectangle |x| <= hx, |y| <= hy and its outward unit normal there. */
+static double rectSdf(double px, double py, double hx, double hy, double *gx, double *gy) {
+    double qx = fabs(px) - hx, qy = fabs(py) - hy, sx = px < 0 ? -1.0 : 1.0, sy = py < 0 ? -1.0 : 1.0;
+    if (qx <= 0 && qy <= 0) {               /* inside: leave through the nearer side */
+        if (qx > qy) { *gx = sx; *gy = 0; return qx; }
+        *gx = 0; *gy = sy; return qy;
+    }
+    double ox = fmax(qx, 0.0), oy = fmax(qy, 0.0), d = sqrt(ox * ox + oy * oy);
+    *gx = sx * ox / d; *gy = sy * oy / d;
+    return d;
+}
+/* Two solid cylinders whose axes AND centres lie in one plane (the left and right hip motors of this robot: both turn about
+ * the trunk's x axis, go1_torque.xml:31-46).  Both shapes are mirror-symmetric about that plane, so a closest pair of points
+ * lies in it and the problem is rectangle vs rectangle (half length along the axis, radius across): the closest pair of two
+ * convex polygons always contains a vertex, so each rectangle's vertex with the smallest signed distance to the OTHER rectangle
+ * is a contact candidate (normal = that rectangle's outward normal there, position half way); each candidate within the margin
+ * becomes a contact (one in general, two in near-symmetric poses).  MuJoCo 2.3.0 sends this pair through libccd's MPR (always
+ * one contact); DESIGN.md section 1, deviation 1.  Returns -1 when the configuration
+ * is not coplanar (no such pair on this robot). */
+static int cylinderCylinderCoplanar(const double *p1, const double *m1, const double *s1, const double *p2, const double *m2, const double *s2,
+                                    double margin, RawCon *con) {
+    double z1[3] = {m1[2], m1[5], m1[8]}, z2[3] = {m2[2], m2[5], m2[8]}, t[3] = {p2[0] - p1[0], p2[1] - p1[1], p2[2] - p1[2]};
+    double nrm[3], e2[3];
+    cross3(nrm, z1, z2);
+    if (norm3(nrm) < 1e-6) cross3(nrm, z1, t);                                  /* parallel axes */
+    if (norm3(nrm) < 1e-9) { nrm[0] = m1[0]; nrm[1] = m1[3]; nrm[2] = m1[6]; }    /* coaxial: any direction across the axis */
+    normalize3(nrm);
+    if (fabs(dot3(nrm, t)) > 1e-6 || fabs(dot3(nrm, z2)) > 1e-6) return -1;
+    cross3(e2, nrm, z1);
+    double cx = dot3(t, z1), cy = dot3(t, e2), ax = dot3(z2, z1), ay = dot3(z2, e2);       /* rectangle 2 in the frame of rectangle 1 */
+    /* the deepest vertex of EACH rectangle in the other one gives a contact of its own (no minimum over the two families: in the
+     * mirror-symmetric pose, both hips at the same limit, the two candidates tie and rounding would pick the normal) */
+    double best[2] = {1e30, 1e30}, bn[2][2] = {{0, 0}, {0, 0}}, bp[2][2] = {{0, 0}, {0, 0}};
+    for (int k = 0; k < 4; k++) {           /* vertices of rectangle 2 against rectangle 1 */
+        double u = (k & 2) ? -s2[1] : s2[1], v = (k & 1) ? -s2[0] : s2[0];
+        double vx = cx + u * ax - v * ay, vy = cy + u * ay + v * ax, gx, gy;
+        double d = rectSdf(vx, vy, s1[1], s1[0], &gx, &gy);
+        if (d < best[0]) { best[0] = d; bn[0][0] = gx; bn[0][1] = gy; bp[0][0] = vx - 0.5 * d * gx; bp[0][1] = vy - 0.5 * d * gy; }
+    }
+    for (int k = 0; k < 4; k++) {           /* vertices of rectangle 1 against rectangle 2 (in the frame of rectangle 2) */
+        double wx = (k & 2) ? -s1[1] : s1[1], wy = (k & 1) ? -s1[0] : s1[0];
+        double rx = wx - cx, ry = wy - cy, lx = rx * ax + ry * ay, ly = -rx * ay + ry * ax, gx, gy;
+        double d = rectSdf(lx, ly, s2[1], s2[0], &gx, &gy);
+        if (d < best[1]) {
+            double nx = gx * ax - gy * ay, ny = gx * ay + gy * ax;                  /* outward normal of rectangle 2, frame 1 */
+            best[1] = d; bn[1][0] = -nx; bn[1][1] = -ny; bp[1][0] = wx - 0.5 * d * nx; bp[1][1] = wy - 0.5 * d * ny;
+        }
+    }
+    int num = 0;
+    for (int f = 0; f < 2; f++) {
+        if (best[f] > margin) continue;
+        memset(con[num].frame, 0, sizeof con[num].frame);
+        for (int k = 0; k < 3; k++) {
+            con[num].frame[k] = bn[f][0] * z1[k] + bn[f][1] * e2[k];
+            con[num].pos[k] = p1[k] + bp[f][0] * z1[k] + bp[f][1] * e2[k];
+        }
+        con[num].dist = best[f];
+        num++;
+    }
+    return num;
+}
 /* F(t) = squared distance between the capsule-axis point pl + t*al (t in [-1, 1]) and a box / solid cylinder given in ITS frame
  * (cylinder: box == 0, sz = {R, R, h}), g(t) = F'(t) / 2 and g'(t).  F is convex along the line. */
 static void seg_eval(const double *pl, const double *al, const double *sz, int box, double t, double *F, double *g, double *dg) {
@@ -893,23 +954,9 @@ static void collide_pair(O1Data *d, int g1, int g2) {
         else if (t1 == GEOM_CAPSULE && t2 == GEOM_CYLINDER) num = capsuleConvex(p1, m1, s1, p2, m2, s2, 0, margin, raw);
         else if (t1 == GEOM_CAPSULE && t2 == GEOM_BOX) num = capsuleConvex(p1, m1, s1, p2, m2, s2, 1, margin, raw);
         else if (t1 == GEOM_CYLINDER && t2 == GEOM_CYLINDER) {
-            /* hip-vs-hip only (MuJoCo: MPR).  Separating-axis tests with the cylinders' support functions along the centre
-             * line, both axes and their cross product; a pair none of them separates (rear hip motors with both abduction
-             * joints within ~0.1 rad of their opposite limits) is COUNTED in warn_unsupported_pair, not collided */
-            double ax4[4][3];
-            double len = sqrt(dot3(t, t));
-            if (len < mjMINVAL) { d->warn_unsupported_pair++; return; }
-            for (int k = 0; k < 3; k++) { ax4[0][k] = t[k] / len; ax4[1][k] = z1[k]; ax4[2][k] = z2[k]; }
-            cross3(ax4[3], z1, z2);
-            if (normalize3(ax4[3]) < 1e-9) memcpy(ax4[3], ax4[0], 24);
-            for (int a = 0; a < 4; a++) {
-                const double *u = ax4[a];
-                double c1 = dot3(z1, u), c2 = dot3(z2, u);
-                double reach = s1[1] * fabs(c1) + s1[0] * sqrt(fmax(0.0, 1 - c1 * c1)) + s2[1] * fabs(c2) + s2[0] * sqrt(fmax(0.0, 1 - c2 * c2));
-                if (fabs(dot3(t, u)) - reach > margin) return;
-            }
-            d->warn_unsupported_pair++;
-            return;
+            /* hip motor vs hip motor (MuJoCo: MPR): exact for this robot's coplanar pairs, anything else is COUNTED, not collided */
+            num = cylinderCylinderCoplanar(p1, m1, s1, p2, m2, s2, margin, raw);
+            if (num < 0) { d->warn_unsupported_pair++; return; }
         }
         else { d->warn_unsupported_pair++; return; }   /* cylinder-box / box-box: no such non-adjacent pair on this robot */
     }

@@ -19,7 +19,7 @@ constexpr int GMAX = 12;      // collision geoms handled by one lane (its leg's 
 constexpr int CMAX = 16;      // active contacts kept per lane
 constexpr int NCLS = 8;       // distinct contact parameter classes (floor-mixed + robot-robot mixed)
 constexpr int NKIND = 4;      // distinct per-geom contact parameter sets
-constexpr int NGP = 704;      // candidate geom pairs of the robot-robot collision (bodies not parent and child, no cylinder-cylinder)
+constexpr int NGP = 704;      // candidate geom pairs of the robot-robot collision (bodies not parent and child; cylinder-cylinder: left / right hips only)
 constexpr int GFLAT = 44;     // robot collision geoms (flat list, sorted by body)
 
 // index tables of the block-arrow layout tt[21] | tk[4][6][3] | kk[4][6]  (go1_warp.cuh)
@@ -426,10 +426,16 @@ inline bool build_dev_model(const void* data, size_t nbytes, DevModel<double>& M
                 if (parent(b) == a || parent(a) == b) continue;
                 for (int g1 = body_g0[a]; g1 < body_g0[a + 1]; g1++)
                     for (int g2 = body_g0[b]; g2 < body_g0[b + 1]; g2++) {
-                        // cylinder-cylinder (hip motor vs hip motor; MuJoCo: MPR) is not collided: DESIGN.md states the reach of that pair
-                        if (M.flat[g1].type == G_CYLINDER && M.flat[g2].type == G_CYLINDER) continue;
+                        // cylinder-cylinder: only the left / right hip motors can meet (coplanar pair, go1_pair.cuh:pp_cyl_cyl); the
+                        // other cylinder pairs (front vs rear hips) are 0.37 m apart and are left out of the table
+                        const bool cc = M.flat[g1].type == G_CYLINDER && M.flat[g2].type == G_CYLINDER;
+                        if (cc) {
+                            const bool hips = (a - 1) % 3 == 0 && (b - 1) % 3 == 0 && a >= 1;
+                            const int la = (a - 1) / 3, lb = (b - 1) / 3;           // legs FR FL RR RL
+                            if (!(hips && la / 2 == lb / 2)) continue;
+                        }
                         const int lo = std::min(M.flat[g1].type, M.flat[g2].type), hi = std::max(M.flat[g1].type, M.flat[g2].type);
-                        GO1_REQ(lo == G_SPHERE || lo == G_CAPSULE, "robot-robot pair without a sphere or capsule is not implemented");
+                        GO1_REQ(cc || lo == G_SPHERE || lo == G_CAPSULE, "robot-robot pair without a sphere or capsule is not implemented");
                         (void)hi;
                         GO1_REQ(M.ngp < NGP, "too many candidate geom pairs");
                         M.gp_a[M.ngp] = (unsigned char)g1; M.gp_b[M.ngp] = (unsigned char)g2; M.ngp++;

@@ -5,6 +5,7 @@
 //   sphere-sphere, sphere-capsule, capsule-capsule, sphere-box      MuJoCo's analytic functions (engine_collision_primitive.c / _box.c)
 //   sphere-cylinder                                                  exact closest feature, one contact (MuJoCo 2.3.0: MPR, tolerance 1e-6)
 //   capsule-cylinder, capsule-box                                    centre (box: long patches both ends) of the contact patch of the capsule axis, see seg_patch
+//   cylinder-cylinder (left vs right hip motors, coplanar)           rectangle vs rectangle in the common plane, see pp_cyl_cyl (MuJoCo: MPR)
 // The normal points from geom1 to geom2, geom1 being the geom of the lower type (mj_collideGeoms' swap).
 #pragma once
 
@@ -296,6 +297,68 @@ GO1_DEV void pp_capsule_capsule(const GeomW<T>& a, const GeomW<T>& b, T margin, 
     }
 }
 
+// signed distance of the 2-D point (px, py) to the rectangle |x| <= hx, |y| <= hy and its outward unit normal there
+template <typename T> GO1_DEV T rect_sdf(T px, T py, T hx, T hy, T& gx, T& gy) {
+    typedef Num<T> N;
+    const T qx = N::abs_(px) - hx, qy = N::abs_(py) - hy, sx = px < 0 ? T(-1) : T(1), sy = py < 0 ? T(-1) : T(1);
+    if (qx <= 0 && qy <= 0) {
+        if (qx > qy) { gx = sx; gy = 0; return qx; }
+        gx = 0; gy = sy; return qy;
+    }
+    const T ox = N::max_(qx, T(0)), oy = N::max_(qy, T(0)), d = N::sqrt_(ox * ox + oy * oy), inv = T(1) / d;
+    gx = sx * ox * inv; gy = sy * oy * inv;
+    return d;
+}
+
+// Two solid cylinders with coplanar axes and centres (left / right hip motors: both turn about the trunk's x axis): rectangle vs
+// rectangle in that plane, one contact per rectangle whose deepest vertex is within the margin of the other one (oracle:
+// cylinderCylinderCoplanar; MuJoCo 2.3.0: MPR, always one contact).  No other cylinder pair of this robot passes the bounding-sphere test.
+template <typename T>
+GO1_DEV void pp_cyl_cyl(const GeomW<T>& a, const GeomW<T>& b, T margin, T inc, Stage2<T>& st) {
+    typedef Num<T> N;
+    const T t[3] = {b.c[0] - a.c[0], b.c[1] - a.c[1], b.c[2] - a.c[2]};
+    T nrm[3], e2[3];
+    cross3(nrm, a.z, b.z);
+    if (dot3(nrm, nrm) < T(1e-12)) cross3(nrm, a.z, t);
+    if (dot3(nrm, nrm) < T(1e-18)) { nrm[0] = a.x[0]; nrm[1] = a.x[1]; nrm[2] = a.x[2]; }
+    normalize3_(nrm);
+    cross3(e2, nrm, a.z);
+    const T cx = dot3(t, a.z), cy = dot3(t, e2), ax = dot3(b.z, a.z), ay = dot3(b.z, e2);
+    // the deepest vertex of EACH rectangle in the other one is a contact of its own (no minimum over the two families: they tie
+    // in the mirror-symmetric pose and rounding would pick the normal)
+    T best = T(1e30), bnx = 0, bny = 0, bpx = 0, bpy = 0;
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        const T u = (k & 2) ? -b.s[1] : b.s[1], v = (k & 1) ? -b.s[0] : b.s[0];
+        const T vx = cx + u * ax - v * ay, vy = cy + u * ay + v * ax;
+        T gx, gy;
+        const T d = rect_sdf(vx, vy, a.s[1], a.s[0], gx, gy);
+        if (d < best) { best = d; bnx = gx; bny = gy; bpx = vx - T(0.5) * d * gx; bpy = vy - T(0.5) * d * gy; }
+    }
+    if (best <= margin && best < inc) {
+        const T n[3] = {bnx * a.z[0] + bny * e2[0], bnx * a.z[1] + bny * e2[1], bnx * a.z[2] + bny * e2[2]};
+        const T pos[3] = {a.c[0] + bpx * a.z[0] + bpy * e2[0], a.c[1] + bpx * a.z[1] + bpy * e2[1], a.c[2] + bpx * a.z[2] + bpy * e2[2]};
+        stage2_emit(st, pos, n, best);
+    }
+    best = T(1e30);
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        const T wx = (k & 2) ? -a.s[1] : a.s[1], wy = (k & 1) ? -a.s[0] : a.s[0];
+        const T rx = wx - cx, ry = wy - cy, lx = rx * ax + ry * ay, ly = -rx * ay + ry * ax;
+        T gx, gy;
+        const T d = rect_sdf(lx, ly, b.s[1], b.s[0], gx, gy);
+        if (d < best) {
+            const T nx = gx * ax - gy * ay, ny = gx * ay + gy * ax;
+            best = d; bnx = -nx; bny = -ny; bpx = wx - T(0.5) * d * nx; bpy = wy - T(0.5) * d * ny;
+        }
+    }
+    if (best <= margin && best < inc) {
+        const T n[3] = {bnx * a.z[0] + bny * e2[0], bnx * a.z[1] + bny * e2[1], bnx * a.z[2] + bny * e2[2]};
+        const T pos[3] = {a.c[0] + bpx * a.z[0] + bpy * e2[0], a.c[1] + bpx * a.z[1] + bpy * e2[1], a.c[2] + bpx * a.z[2] + bpy * e2[2]};
+        stage2_emit(st, pos, n, best);
+    }
+}
+
 // narrowphase dispatch for an ordered pair (type(a) <= type(b)); returns false for a type pair that is not implemented
 template <typename T>
 GO1_DEV bool pp_collide(const GeomW<T>& a, const GeomW<T>& b, T margin, T inc, Stage2<T>& st) {
@@ -317,6 +380,7 @@ GO1_DEV bool pp_collide(const GeomW<T>& a, const GeomW<T>& b, T margin, T inc, S
         else pp_capsule_convex(a, b, b.type == G_BOX, margin, inc, st);
         return true;
     }
+    if (a.type == G_CYLINDER && b.type == G_CYLINDER) { pp_cyl_cyl(a, b, margin, inc, st); return true; }
     return false;
 }
 

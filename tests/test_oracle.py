@@ -152,6 +152,27 @@ def test_oracle_reproduces_golden_trace(ctrl):
         assert sim.data.ncon == post["ncon"][t]
 
 
+@pytest.mark.parametrize("ctrl", ["torque", "position"])
+def test_every_robot_pair_of_the_golden_states_is_collided(ctrl):
+    """The oracle COUNTS a geom pair it cannot collide (warn_unsupported_pair: a cylinder pair that is not coplanar, cylinder-box,
+    box-box) instead of silently skipping it: no state of the golden sets holds one, and the random-torque sets do exercise the one
+    cylinder-cylinder case this robot has (left vs right rear hip motor)."""
+    m = Model.from_blob(pc.model_blob(ctrl))
+    gt = np.asarray(m.geom_type)
+    sim = OracleSim(m)
+    n_states = n_cylcyl = 0
+    for pre, post in (pc.load_trace(ctrl), pc.load_starts(ctrl)):
+        for t in range(len(post["reward"])):
+            sim.reset_data()
+            sim.data.qpos[:] = pre["qpos"][t]; sim.data.qvel[:] = pre["qvel"][t]
+            sim.data.ctrl[:] = post["action"][t]
+            sim.step(1)
+            n_states += 1
+            n_cylcyl += sum(1 for c in sim.data.contact if c.geom1 > 0 and gt[c.geom1] == 5 and gt[c.geom2] == 5)
+    assert n_states > 800 and sim.data.warn_unsupported_pair == 0
+    assert n_cylcyl > 0 or ctrl == "position"
+
+
 def test_substep_golden_is_consistent_with_trace():
     sub = np.load(os.path.join(pc.GOLDEN, "substeps_torque.npz"))
     pre, post = pc.load_trace("torque")

@@ -34,7 +34,7 @@ ALG_FLOP_PER_ENV_STEP = 0.67e6     # SURVEY 8(d) nominal (10 substeps x (25k + 3
 # FP32 operations the kernel actually EXECUTES per env-step (fadd + fmul + 2 ffma, predicated-on threads) in the committed
 # ncu capture (profiles/r1_ncu_k_step_final_raw_selected.txt): 1.885e10 per launch of 16384 envs; 3.7 iterations per substep
 # instead of the nominal 3 and the redundancy of lane-parallel evaluation make up the difference to the nominal figure
-NCU_EXECUTED_FLOP_PER_ENV_STEP = 1.31e6     # profiles/r2_ncu_k_step_final_raw_selected.txt (round 1, floor contacts only: 1.15e6)
+NCU_EXECUTED_FLOP_PER_ENV_STEP = 1.32e6     # profiles/r2_ncu_k_step_final_raw_selected.txt (round 1, floor contacts only: 1.15e6)
 FP32_FMA_MEASURED_TFLOPS = 72.1    # tools/ubench/fma.cu on this pool's B200 (148 SMs, 1965 MHz): 97 % of 148 x 128 x 2 x 1.965 GHz
 BURNIN_FALL, BURNIN_MIX = 300, 100   # untimed control steps before / after the episode phases are staggered (see burn_in)
 STATS_EVERY = 100                    # BASELINE config 4: the rollout statistics are all-reduced every 100 control steps

@@ -272,6 +272,8 @@ class DevicePPO:
         N = batch["obs"].shape[0]
         mb = N // hp["n_minibatches"]
         diag = None
+        with torch.no_grad():
+            vl_before = ((self.net.value(batch["obs"]) - batch["ret"]) ** 2).mean()
         for _ in range(hp["n_epochs"]):
             perm = torch.randperm(N, device=self.device)
             for k in range(hp["n_minibatches"]):
@@ -284,6 +286,10 @@ class DevicePPO:
                     allreduce_grads(self.params, self.world)
                 nn.utils.clip_grad_norm_(self.params, hp["max_grad_norm"])
                 self.opt.step()
+        with torch.no_grad():       # SB3 logs train/explained_variance the same way (ppo.py:train)
+            res = batch["ret"] - self.net.value(batch["obs"])
+            diag["value_loss_before"], diag["value_loss_after"] = vl_before, (res ** 2).mean()
+            diag["explained_variance"] = 1 - res.var() / batch["ret"].var().clamp_min(1e-12)
         return diag
 
     def learn(self, total_timesteps: int, callback: Optional[Callable[[dict], bool]] = None, log: bool = True):
@@ -302,7 +308,9 @@ class DevicePPO:
             rec = dict(iteration=len(self.history) + 1, timesteps=self.num_timesteps, mean_step_reward=s[2] / s[3], episodes=int(s[1]),
                        mean_episode_return=(s[0] / s[1]) if s[1] > 0 else None, fps=(self.num_timesteps - start) / (time.time() - t0),
                        policy_loss=float(diag["policy_loss"]), value_loss=float(diag["value_loss"]), approx_kl=float(diag["approx_kl"]),
-                       clip_fraction=float(diag["clip_fraction"]), std=float(self.net.log_std.detach().exp().mean()))
+                       clip_fraction=float(diag["clip_fraction"]), std=float(self.net.log_std.detach().exp().mean()),
+                       value_loss_before=float(diag["value_loss_before"]), value_loss_after=float(diag["value_loss_after"]),
+                       explained_variance=float(diag["explained_variance"]))
             self.history.append(rec)
             if log and self.rank == 0:
                 print(rec, flush=True)

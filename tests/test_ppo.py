@@ -190,7 +190,9 @@ def test_device_ppo_learns_and_round_trips(cuda_lib_f32, tmp_path):
     assert len(h) == 3 and h[-1]["timesteps"] == 3 * 16 * 2048
     assert all(np.isfinite(r["policy_loss"]) and np.isfinite(r["value_loss"]) for r in h)
     assert 0 <= h[0]["approx_kl"] < 0.1 and h[0]["clip_fraction"] < 0.5
-    assert h[-1]["value_loss"] < h[0]["value_loss"]                     # the critic fits the returns of a random policy quickly
+    # every update lowers the critic's error on the batch it was computed from (the returns themselves grow from iteration to
+    # iteration while the episodes get longer, so losses of different iterations are not comparable)
+    assert all(r["value_loss_after"] < r["value_loss_before"] for r in h)
     path = m.save(str(tmp_path / "ppo_b200"))
     m2 = ppo.DevicePPO.load(path, env)
     obs = np.random.default_rng(0).normal(size=(8, 48))

@@ -185,6 +185,19 @@ int go1_reset(go1_handle h, const uint8_t* mask_dev, float* obs_dev, void* strea
 int go1_step(go1_handle h, const float* actions_dev, float* obs_dev, float* rew_dev, uint8_t* done_dev,
              uint8_t* trunc_dev, float* terminal_obs_dev, float* info_dev, void* stream);
 
+/* go1_step without any allocation on the call path.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot reach cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).  Same arguments,
+ * same results as go1_step, bit for bit; the step kernel's scratch (claim counter of the work queue, queue order, per-environment
+ * work keys) lives in one file-scope `static __device__` array of the library instead of the handle's buffers, 128 KB that every
+ * GPU which loads the library holds until exit.  Limit: handles of at most GO1_NOALLOC_MAX_ENVS environments (GO1_EINVAL with a
+ * message otherwise).  The call performs no cudaMalloc / cudaFree / allocating library routine (the handle itself is created
+ * beforehand by go1_create, which does allocate).  ALL handles on one device share the array: calls that overlap on the GPU
+ * (different streams, or another host thread's handle) race on it -- serialise them.  The array keeps the previous call's work
+ * keys on purpose (a sorting hint only: results do not depend on it); the claim counter is cleared by every call. */
+#define GO1_NOALLOC_MAX_ENVS 16384
+int go1_step_noalloc(go1_handle h, const float* actions_dev, float* obs_dev, float* rew_dev, uint8_t* done_dev,
+                     uint8_t* trunc_dev, float* terminal_obs_dev, float* info_dev, void* stream);
+
 /* same with HOST buffers: H2D of actions, kernel, D2H of results, synchronous (the VecEnv path). */
 int go1_step_host(go1_handle h, const float* actions, float* obs, float* rew, uint8_t* done, uint8_t* trunc,
                   float* terminal_obs, float* info);

@@ -20,6 +20,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -887,6 +888,75 @@ int go1_step(go1_handle h, const float* actions_dev, float* obs_dev, float* rew_
     P.term_obs = terminal_obs_dev; P.info = info_dev;
     h->launch_counter++;
     return launch(h, P, stream ? (cudaStream_t)stream : h->stream);
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// go1_step_noalloc: go1_step for callers that must not reach a device allocator (CUDA graph capture, tight serving loops).
+// The step kernel's scratch -- the claim counter of the persistent work queue, the queue order k_order writes and the per-environment
+// work keys k_step leaves for the next order -- lives in ONE file-scope device array instead of the handle's cudaMalloc'ed
+// buffers.  Every handle on a device shares it: calls that overlap on the GPU (two streams) race on it.  The array keeps the last
+// call's contents: the counter is cleared by every call; the work keys are deliberately NOT (they are only a sorting hint; k_order
+// clamps whatever it finds and emits a valid permutation, and the results of a step do not depend on the queue order).
+// In host code `g_noalloc_scratch` is a host-side stand-in for the symbol, not a device address: the address the kernels get comes
+// from cudaGetSymbolAddress, once per device, with that device current.
+constexpr int NOALLOC_HDR = 64;      // ints before the two arrays (the queue counter is word 0): keeps the arrays 256-byte aligned
+#ifdef GO1_EMU
+alignas(256) static int g_noalloc_scratch[NOALLOC_HDR + 2 * GO1_NOALLOC_MAX_ENVS];      // CPU emulation build (tests only): plain host memory
+#else
+static __device__ __align__(256) int g_noalloc_scratch[NOALLOC_HDR + 2 * GO1_NOALLOC_MAX_ENVS];      // 128.25 KB per GPU that loads the library
+#endif
+static std::mutex g_noalloc_mu;
+static int* g_noalloc_dev[64] = {};  // device address of g_noalloc_scratch, per device ordinal
+
+static int noalloc_scratch(go1_handle h, int** out) {
+    if (h->device < 0 || h->device >= 64) { h->err = "go1_step_noalloc: device ordinal beyond 63"; return GO1_EINVAL; }
+    std::lock_guard<std::mutex> lk(g_noalloc_mu);
+    if (!g_noalloc_dev[h->device]) {
+#ifdef GO1_EMU
+        g_noalloc_dev[h->device] = g_noalloc_scratch;      // CPU emulation build (tests only): device memory is host memory
+#else
+        void* ptr = nullptr;
+        cudaError_t e = cudaGetSymbolAddress(&ptr, g_noalloc_scratch);      // current device = h->device (set by the caller below)
+        if (e != cudaSuccess || !ptr) {
+            h->err = std::string("go1_step_noalloc: cudaGetSymbolAddress failed: ") + cudaGetErrorString(e);
+            return GO1_ECUDA;
+        }
+        g_noalloc_dev[h->device] = (int*)ptr;
+#endif
+    }
+    *out = g_noalloc_dev[h->device];
+    return GO1_OK;
+}
+
+int go1_step_noalloc(go1_handle h, const float* actions_dev, float* obs_dev, float* rew_dev, uint8_t* done_dev, uint8_t* trunc_dev,
+                     float* terminal_obs_dev, float* info_dev, void* stream) {
+    if (!h || !actions_dev || !obs_dev || !rew_dev || !done_dev || !trunc_dev) { if (h) h->err = "go1_step_noalloc: null buffer"; return GO1_EINVAL; }
+    if (h->n_envs > GO1_NOALLOC_MAX_ENVS) {
+        h->err = "go1_step_noalloc: the handle has " + std::to_string(h->n_envs) + " environments, the static scratch holds GO1_NOALLOC_MAX_ENVS = " +
+                 std::to_string(GO1_NOALLOC_MAX_ENVS) + " (use go1_step, or several handles stepped one after the other)";
+        return GO1_EINVAL;
+    }
+    CK(cudaSetDevice(h->device));
+    int* sc = nullptr;
+    const int rc = noalloc_scratch(h, &sc);
+    if (rc != GO1_OK) return rc;
+    KParams<real> P = base_params(h);
+    P.queue = sc; P.order = sc + NOALLOC_HDR; P.work = sc + NOALLOC_HDR + GO1_NOALLOC_MAX_ENVS;
+    P.actions = actions_dev; P.action_mode = 0; P.obs = obs_dev; P.rew = rew_dev; P.done = done_dev; P.trunc = trunc_dev;
+    P.term_obs = terminal_obs_dev; P.info = info_dev;
+    h->launch_counter++;
+    cudaStream_t s = stream ? (cudaStream_t)stream : h->stream;
+    int grid = (h->n_envs + GO1_WARPS - 1) / GO1_WARPS;
+    if (grid > h->grid_blocks) grid = h->grid_blocks;
+    CK(cudaMemsetAsync(P.queue, 0, sizeof(int), s));        // the claim counter must start at zero; nothing else has to
+#ifdef GO1_EMU
+    GO1_LAUNCH(k_order, 1, 32, 0, s, (const int*)P.work, sc + NOALLOC_HDR, h->n_envs);
+#else
+    GO1_LAUNCH(k_order, 1, 1024, 0, s, (const int*)P.work, sc + NOALLOC_HDR, h->n_envs);
+#endif
+    GO1_LAUNCH(k_step<real>, grid, GO1_WARPS * 32, step_smem_bytes(), s, P);
+    CK(cudaGetLastError());
+    return GO1_OK;
 }
 
 // true when [p, p + bytes) lies inside a buffer the caller page-locked with go1_host_register: DMA goes straight to it

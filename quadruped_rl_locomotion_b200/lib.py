@@ -85,7 +85,7 @@ EXPORTS = (
     "go1_num_envs", "go1_action_bounds", "go1_reset", "go1_step", "go1_step_host", "go1_step_host_f64", "go1_reset_host", "go1_rollout", "go1_policy_act",
     "go1_last_rollout_timing", "go1_set_state", "go1_get_state", "go1_enable_diag", "go1_get_diag",
     "go1_get_contacts", "go1_set_attr_f32", "go1_get_attr_f32", "go1_biped_info_host", "go1_biped_info_dev",
-    "go1_host_register", "go1_host_unregister", "go1_stagger_phases", "go1_policy_forward", "go1_policy_act_scalar", "go1_render",
+    "go1_host_register", "go1_host_unregister", "go1_stagger_phases", "go1_step_noalloc", "go1_policy_forward", "go1_policy_act_scalar", "go1_render",
 )
 
 
@@ -118,6 +118,7 @@ class Go1Lib:
         L.go1_action_bounds.argtypes = [vp, C.POINTER(C.c_float), C.POINTER(C.c_float)]
         L.go1_reset.argtypes = [vp, u8p, f32p, vp]
         L.go1_step.argtypes = [vp, f32p, f32p, f32p, u8p, u8p, f32p, f32p, vp]
+        L.go1_step_noalloc.argtypes = [vp, f32p, f32p, f32p, u8p, u8p, f32p, f32p, vp]
         L.go1_step_host.argtypes = [vp, f32p, f32p, f32p, u8p, u8p, f32p, f32p]
         L.go1_step_host_f64.argtypes = [vp, f32p, C.c_void_p, f32p, u8p, u8p, f32p, f32p]
         L.go1_reset_host.argtypes = [vp, u8p, f32p]
@@ -210,6 +211,12 @@ class Sim:
     def step(self, actions, obs, rew, done, trunc, terminal_obs=None, info=None, stream=None):
         self._check(self.lib.L.go1_step(self._h, _ptr(actions), _ptr(obs), _ptr(rew), _ptr(done), _ptr(trunc),
                                         _ptr(terminal_obs), _ptr(info), stream), "go1_step")
+
+    def step_noalloc(self, actions, obs, rew, done, trunc, terminal_obs=None, info=None, stream=None):
+        """``go1_step`` with the kernel's scratch in the library's static device array (``go1_step_noalloc``): no allocation on the
+        call path, at most ``NOALLOC_MAX_ENVS`` environments, calls on one device must not overlap."""
+        self._check(self.lib.L.go1_step_noalloc(self._h, _ptr(actions), _ptr(obs), _ptr(rew), _ptr(done), _ptr(trunc),
+                                                _ptr(terminal_obs), _ptr(info), stream), "go1_step_noalloc")
 
     # -- host-buffer API (numpy, C-contiguous)
     def step_host(self, actions, obs, rew, done, trunc, terminal_obs=None, info=None):

@@ -1,18 +1,22 @@
 // go1_policy_tc.cuh -- the SB3 MlpPolicy forward (reference train.py:122-128: actor 48-64-64-12 + critic 48-64-64-1, tanh) as a
 // batched GEMM over all environments on the 5th-generation tensor cores (row a21 of the scope table).
 //
-// One CTA = 128 environments = the M dimension of tcgen05.mma (cta_group::1, M = 128).  kind::tf32: the operands are the fp32
+// One tile = 128 environments = the M dimension of tcgen05.mma (cta_group::1, M = 128).  kind::tf32: the operands are the fp32
 // observations / weights / activations as they lie in shared memory (the tensor core reads the upper 19 bits: 10-bit mantissa),
-// accumulation in fp32 in tensor memory.  Three MMA groups, each followed by an epilogue in which thread t owns row t of the
-// accumulator (TMEM lane t, read with tcgen05.ld 32x32b).  Operands are rounded to tf32 (round-to-nearest) when they are staged:
+// accumulation in fp32 in tensor memory.  Three MMA groups per tile, each followed by an epilogue in which thread t owns row t of
+// the accumulator (TMEM lane t, read with tcgen05.ld 32x32b).  Operands are rounded to tf32 (round-to-nearest) when they are staged:
 //   1. [128 x 48] x [48 x 128]   actor and critic first layers side by side (N = 128)      -> + bias, tanh -> H1a | H1c
 //   2. H1a [128 x 64] x W1a', H1c x W1c'   (two N = 64 groups into TMEM columns 0..63 | 64..127)   -> + bias, tanh -> H2a | H2c
 //   3. H2a x W2a' (N = 16: 12 action means), H2c x W2c' (N = 16: value in column 0)         -> + bias, Gaussian sample (Philox),
 //      clip to the action bounds, log-probability, value
+// Persistent CTAs of 256 threads = two groups of four warps.  The weights (64 KB for actor + critic) are staged ONCE per CTA; each
+// group then walks its own sequence of tiles with its own activations (64 KB), 128 TMEM columns, mbarrier and named barrier, so the
+// epilogue (TMEM loads, tanh, shared-memory stores) of one group overlaps the MMAs and the observation loads of the other.
 // Operand layout in shared memory: the canonical K-major no-swizzle layout of the matrix descriptor -- 8 x 16-byte core matrices
 // (8 rows x 4 tf32), core matrices of one 8-row group contiguous along K (leading byte offset 128), 8-row groups K/4 * 128 bytes
-// apart (stride byte offset).  The weights (62 KB for actor + critic) are staged once per CTA; nothing but the observations is
-// read from HBM per environment and nothing but actions / value / log-prob is written.
+// apart (stride byte offset).  Staging walks that layout linearly (float4 number i goes to byte 16 i), so the shared-memory stores
+// are conflict-free; nothing but the observations is read from HBM per environment and nothing but actions / value / log-prob
+// is written.
 #pragma once
 #include <cstdint>
 
@@ -83,50 +87,97 @@ __device__ __forceinline__ void ld16(uint32_t taddr, float* v) {
 template <int KTOT> __device__ __forceinline__ int op_off(int row, int k) {
     return (row >> 3) * (KTOT / 4) * 128 + (k >> 2) * 128 + (row & 7) * 16 + (k & 3) * 4;
 }
+// float4 number i of a K-major operand with KTOT columns lies at byte 16 i; it holds row r, columns 4 kc .. 4 kc + 3
+template <int KTOT> __device__ __forceinline__ void unit_rc(int i, int& r, int& kc) {
+    const int grp = i >> 3;
+    r = (grp / (KTOT / 4)) * 8 + (i & 7);
+    kc = grp % (KTOT / 4);
+}
+__device__ __forceinline__ float4 load4(const float* p, bool aligned) {
+    if (aligned) return *reinterpret_cast<const float4*>(p);
+    return make_float4(p[0], p[1], p[2], p[3]);
+}
+__device__ __forceinline__ float4 tf32x4(float4 v) { return make_float4(to_tf32(v.x), to_tf32(v.y), to_tf32(v.z), to_tf32(v.w)); }
 // stage a row-major fp32 matrix w[rows][K] (torch [out][in] layout; rows beyond `rows_valid` are zero) as an operand
 template <int KTOT> __device__ __forceinline__ void stage(unsigned char* dst, const float* w, int rows, int rows_valid, int tid, int nthreads) {
-    for (int i = tid; i < rows * KTOT; i += nthreads) {
-        const int r = i / KTOT, k = i - r * KTOT;
-        *reinterpret_cast<float*>(dst + op_off<KTOT>(r, k)) = (w != nullptr && r < rows_valid) ? to_tf32(w[(size_t)r * KTOT + k]) : 0.0f;
+    const bool al = (reinterpret_cast<uintptr_t>(w) & 15) == 0;
+    for (int i = tid; i < rows * (KTOT / 4); i += nthreads) {
+        int r, kc;
+        unit_rc<KTOT>(i, r, kc);
+        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (w != nullptr && r < rows_valid) v = tf32x4(load4(w + (size_t)r * KTOT + 4 * kc, al));
+        *reinterpret_cast<float4*>(dst + 16 * i) = v;
     }
 }
+// tanh through one MUFU.EX2 and one MUFU.RCP: |error| < 3e-7 absolute, far below the tf32 rounding (5e-4) applied to the result
+__device__ __forceinline__ float tanh_fast(float x) { return 1.0f - __fdividef(2.0f, __expf(2.0f * x) + 1.0f); }
 
-// shared-memory plan (bytes)
-constexpr int SM_OBS = 0;                               // A1  [128 x 48]
-constexpr int SM_HA = SM_OBS + 128 * 48 * 4;            // A2a [128 x 64]
-constexpr int SM_HC = SM_HA + 128 * 64 * 4;             // A2c [128 x 64]
-constexpr int SM_B1 = SM_HC + 128 * 64 * 4;             // [W0a; W0c]  [128 x 48]
+// shared-memory plan (bytes): weights and biases once per CTA, activations per group
+constexpr int SM_B1 = 0;                                // [W0a; W0c]  [128 x 48]
 constexpr int SM_W1A = SM_B1 + 128 * 48 * 4;            // [64 x 64]
 constexpr int SM_W1C = SM_W1A + 64 * 64 * 4;
 constexpr int SM_W2A = SM_W1C + 64 * 64 * 4;            // [16 x 64] (12 valid rows)
 constexpr int SM_W2C = SM_W2A + 16 * 64 * 4;            // [16 x 64] (1 valid row)
-constexpr int SM_BIAS = SM_W2C + 16 * 64 * 4;           // b0a 64 | b0c 64 | b1a 64 | b1c 64 | b2a 16 | b2c 16 | log_std 16 | lo 16 | hi 16
-constexpr int SM_BAR = SM_BIAS + (4 * 64 + 5 * 16) * 4; // mbarrier (8 B) + TMEM base (4 B)
-constexpr int SM_TOTAL = SM_BAR + 16;
+constexpr int SM_ACT = SM_W2C + 16 * 64 * 4;            // group g: HA [128 x 64] (the observation tile [128 x 48] aliases it) | HC [128 x 64]
+constexpr int ACT_BYTES = 2 * 128 * 64 * 4;
+constexpr int SM_BIAS = SM_ACT + 2 * ACT_BYTES;         // b0a 64 | b0c 64 | b1a 64 | b1c 64 | b2a 16 | b2c 16 | log_std 16 | lo 16 | hi 16
+constexpr int SM_BAR = SM_BIAS + (4 * 64 + 5 * 16) * 4; // 2 mbarriers (8 B each) + TMEM base (4 B)
+constexpr int SM_TOTAL = SM_BAR + 32;
+constexpr int THREADS = 256;
+
+__device__ __forceinline__ void group_sync(int g) { asm volatile("bar.sync %0, 128;" :: "r"(1 + g) : "memory"); }
+// shared-memory writes of this group -> visible to the tensor core; TMEM reads of this group ordered before the MMAs that follow
+__device__ __forceinline__ void handoff(int g) {
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    group_sync(g);
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+}
+// epilogue of a hidden layer: TMEM columns [c_lo, c_hi) + bias -> tanh -> tf32 -> HA (columns < 64) / HC in operand layout
+__device__ __forceinline__ void hidden_epilogue(unsigned char* act, uint32_t lane_addr, const float* bias, int c_lo, int c_hi, int row) {
+#pragma unroll 1
+    for (int c0 = c_lo; c0 < c_hi; c0 += 16) {
+        float v[16];
+        ld16(lane_addr + c0, v);
+        unsigned char* dst = act + (c0 < 64 ? 0 : 128 * 64 * 4) + (row >> 3) * (64 / 4) * 128 + (row & 7) * 16;
+#pragma unroll
+        for (int q = 0; q < 4; q++) {
+            const int col = (c0 & 63) + 4 * q;
+            float4 o;
+            o.x = to_tf32(tanh_fast(v[4 * q + 0] + bias[c0 + 4 * q + 0])); o.y = to_tf32(tanh_fast(v[4 * q + 1] + bias[c0 + 4 * q + 1]));
+            o.z = to_tf32(tanh_fast(v[4 * q + 2] + bias[c0 + 4 * q + 2])); o.w = to_tf32(tanh_fast(v[4 * q + 3] + bias[c0 + 4 * q + 3]));
+            *reinterpret_cast<float4*>(dst + (col >> 2) * 128) = o;
+        }
+    }
+}
 
 }  // namespace tc
 
-__global__ void __launch_bounds__(128, 1) k_policy_tc(const __grid_constant__ PolicyTCParams P) {
+__global__ void __launch_bounds__(tc::THREADS, 1) k_policy_tc(const __grid_constant__ PolicyTCParams P) {
     using namespace tc;
     extern __shared__ __align__(1024) unsigned char sm[];
-    const int tid = threadIdx.x, warp = tid >> 5;
+    const int tid = threadIdx.x, warp = tid >> 5, g = tid >> 7, ltid = tid & 127;
     float* bias = reinterpret_cast<float*>(sm + SM_BIAS);
-    const uint32_t bar = smem_u32(sm + SM_BAR);
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(sm + SM_BAR + 8);
-    const int row0 = blockIdx.x * 128;
+    const uint32_t bar = smem_u32(sm + SM_BAR) + 8 * g;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(sm + SM_BAR + 16);
+    const bool critic = P.cw0 != nullptr;
+    const int tiles = (P.n + 127) >> 7;
 
-    // ---- one-time setup: barrier, tensor memory (128 columns x 128 lanes of fp32), weights and biases into shared memory
-    if (tid == 0) { mbar_init(bar, 1); asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+    // ---- one-time setup: barriers, tensor memory (2 x 128 columns x 128 lanes of fp32), weights and biases into shared memory
+    if (tid == 0) {
+        mbar_init(smem_u32(sm + SM_BAR), 1); mbar_init(smem_u32(sm + SM_BAR) + 8, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
     if (warp == 0) {
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" :: "r"(smem_u32(tmem_slot)), "n"(128) : "memory");
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" :: "r"(smem_u32(tmem_slot)), "n"(256) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
-    stage<48>(sm + SM_B1, P.aw0, 64, 64, tid, 128);
-    stage<48>(sm + SM_B1 + 8 * (48 / 4) * 128, P.cw0, 64, 64, tid, 128);      // rows 64..127 = the critic's first layer
-    stage<64>(sm + SM_W1A, P.aw1, 64, 64, tid, 128);
-    stage<64>(sm + SM_W1C, P.cw1, 64, 64, tid, 128);
-    stage<64>(sm + SM_W2A, P.aw2, 16, 12, tid, 128);
-    stage<64>(sm + SM_W2C, P.cw2, 16, 1, tid, 128);
+    stage<48>(sm + SM_B1, P.aw0, 64, 64, tid, THREADS);
+    stage<48>(sm + SM_B1 + 8 * (48 / 4) * 128, P.cw0, 64, 64, tid, THREADS);      // rows 64..127 = the critic's first layer
+    stage<64>(sm + SM_W1A, P.aw1, 64, 64, tid, THREADS);
+    stage<64>(sm + SM_W1C, P.cw1, 64, 64, tid, THREADS);
+    stage<64>(sm + SM_W2A, P.aw2, 16, 12, tid, THREADS);
+    stage<64>(sm + SM_W2C, P.cw2, 16, 1, tid, THREADS);
     if (tid < 64) {
         bias[tid] = P.ab0[tid]; bias[64 + tid] = P.cb0 ? P.cb0[tid] : 0.f;
         bias[128 + tid] = P.ab1[tid]; bias[192 + tid] = P.cb1 ? P.cb1[tid] : 0.f;
@@ -138,125 +189,127 @@ __global__ void __launch_bounds__(128, 1) k_policy_tc(const __grid_constant__ Po
         bias[304 + tid] = tid < 12 ? P.lo[tid] : 0.f;
         bias[320 + tid] = tid < 12 ? P.hi[tid] : 0.f;
     }
-    // observations of this CTA's 128 environments: coalesced global reads, scattered into the operand layout
-    for (int i = tid; i < 128 * 48; i += 128) {
-        const int r = i / 48, k = i - 48 * r;
-        const int e = row0 + r;
-        *reinterpret_cast<float*>(sm + SM_OBS + op_off<48>(r, k)) = e < P.n ? to_tf32(P.obs[(size_t)e * 48 + k]) : 0.f;
-    }
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");        // generic-proxy smem writes -> visible to the tensor core (async proxy)
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-    const uint32_t tmem = *tmem_slot;
-    const uint32_t lane_addr = tmem + ((uint32_t)(warp * 32) << 16);     // this warp's 32 TMEM lanes (rows 32*warp ..)
+    const uint32_t tmem = *tmem_slot + 128 * g;                                       // this group's 128 accumulator columns
+    const uint32_t lane_addr = tmem + ((uint32_t)((warp & 3) * 32) << 16);            // this warp's 32 TMEM lanes (rows 32 (warp % 4) ..)
     const uint32_t sbase = smem_u32(sm);
+    unsigned char* act = sm + SM_ACT + g * ACT_BYTES;
+    const uint32_t s_ha = sbase + SM_ACT + g * ACT_BYTES, s_hc = s_ha + 128 * 64 * 4;
+    const bool obs_al = (reinterpret_cast<uintptr_t>(P.obs) & 15) == 0, act_al = (reinterpret_cast<uintptr_t>(P.act) & 15) == 0;
     uint32_t parity = 0;
 
-    // ---- layer 1: D[128 x 128] = obs[128 x 48] . [W0a; W0c]'
-    if (tid == 0) {
-        const uint32_t idesc = make_idesc_tf32(128, 128);
-#pragma unroll
-        for (int k = 0; k < 48 / 8; k++)
-            mma_tf32(tmem, make_desc(sbase + SM_OBS + k * 256, 128, (48 / 4) * 128), make_desc(sbase + SM_B1 + k * 256, 128, (48 / 4) * 128), idesc, k > 0);
-        commit(bar);
-    }
-    mbar_wait(bar, parity); parity ^= 1;
-    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-    // epilogue: thread = row.  Columns 0..63 -> H1a, 64..127 -> H1c
 #pragma unroll 1
-    for (int c0 = 0; c0 < 128; c0 += 16) {
-        float v[16];
-        ld16(lane_addr + c0, v);
-        unsigned char* dst = sm + (c0 < 64 ? SM_HA : SM_HC);
-#pragma unroll
-        for (int j = 0; j < 16; j++) {
-            const int col = (c0 & 63) + j;
-            *reinterpret_cast<float*>(dst + op_off<64>(tid, col)) = to_tf32(tanhf(v[j] + bias[c0 + j]));
+    for (int tile = blockIdx.x + g * gridDim.x; tile < tiles; tile += 2 * gridDim.x) {
+        const int row0 = tile * 128;
+        // observations of this tile: 16-byte global reads, linear 16-byte shared-memory stores (the region doubles as HA later)
+#pragma unroll 4
+        for (int i = ltid; i < 128 * (48 / 4); i += 128) {
+            int r, kc;
+            unit_rc<48>(i, r, kc);
+            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (row0 + r < P.n) v = tf32x4(load4(P.obs + (size_t)(row0 + r) * 48 + 4 * kc, obs_al));
+            *reinterpret_cast<float4*>(act + 16 * i) = v;
         }
-    }
-    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-    __syncthreads();
-    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        handoff(g);      // also orders the previous tile's TMEM reads before this tile's MMAs
 
-    // ---- layer 2: columns 0..63 = H1a . W1a', columns 64..127 = H1c . W1c'
-    if (tid == 0) {
-        const uint32_t idesc = make_idesc_tf32(128, 64);
+        // ---- layer 1: D[128 x 128] = obs[128 x 48] . [W0a; W0c]'
+        if (ltid == 0) {
+            const uint32_t idesc = make_idesc_tf32(128, critic ? 128 : 64);
 #pragma unroll
-        for (int k = 0; k < 64 / 8; k++)
-            mma_tf32(tmem, make_desc(sbase + SM_HA + k * 256, 128, (64 / 4) * 128), make_desc(sbase + SM_W1A + k * 256, 128, (64 / 4) * 128), idesc, k > 0);
-#pragma unroll
-        for (int k = 0; k < 64 / 8; k++)
-            mma_tf32(tmem + 64, make_desc(sbase + SM_HC + k * 256, 128, (64 / 4) * 128), make_desc(sbase + SM_W1C + k * 256, 128, (64 / 4) * 128), idesc, k > 0);
-        commit(bar);
-    }
-    mbar_wait(bar, parity); parity ^= 1;
-    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-#pragma unroll 1
-    for (int c0 = 0; c0 < 128; c0 += 16) {
-        float v[16];
-        ld16(lane_addr + c0, v);
-        unsigned char* dst = sm + (c0 < 64 ? SM_HA : SM_HC);       // the layer-2 MMAs that read H1 have completed (commit observed)
-#pragma unroll
-        for (int j = 0; j < 16; j++) {
-            const int col = (c0 & 63) + j;
-            *reinterpret_cast<float*>(dst + op_off<64>(tid, col)) = to_tf32(tanhf(v[j] + bias[128 + c0 + j]));
+            for (int k = 0; k < 48 / 8; k++)
+                mma_tf32(tmem, make_desc(s_ha + k * 256, 128, (48 / 4) * 128), make_desc(sbase + SM_B1 + k * 256, 128, (48 / 4) * 128), idesc, k > 0);
+            commit(bar);
         }
-    }
-    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-    __syncthreads();
-    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        mbar_wait(bar, parity); parity ^= 1;
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        hidden_epilogue(act, lane_addr, bias, 0, critic ? 128 : 64, ltid);          // the MMAs that read the observation tile have completed
+        handoff(g);
 
-    // ---- layer 3: columns 0..15 = H2a . W2a' (12 action means), columns 16..31 = H2c . W2c' (value in column 16)
-    if (tid == 0) {
-        const uint32_t idesc = make_idesc_tf32(128, 16);
+        // ---- layer 2: columns 0..63 = H1a . W1a', columns 64..127 = H1c . W1c'
+        if (ltid == 0) {
+            const uint32_t idesc = make_idesc_tf32(128, 64);
 #pragma unroll
-        for (int k = 0; k < 64 / 8; k++)
-            mma_tf32(tmem, make_desc(sbase + SM_HA + k * 256, 128, (64 / 4) * 128), make_desc(sbase + SM_W2A + k * 256, 128, (64 / 4) * 128), idesc, k > 0);
+            for (int k = 0; k < 64 / 8; k++)
+                mma_tf32(tmem, make_desc(s_ha + k * 256, 128, (64 / 4) * 128), make_desc(sbase + SM_W1A + k * 256, 128, (64 / 4) * 128), idesc, k > 0);
+            if (critic) {
 #pragma unroll
-        for (int k = 0; k < 64 / 8; k++)
-            mma_tf32(tmem + 16, make_desc(sbase + SM_HC + k * 256, 128, (64 / 4) * 128), make_desc(sbase + SM_W2C + k * 256, 128, (64 / 4) * 128), idesc, k > 0);
-        commit(bar);
-    }
-    mbar_wait(bar, parity); parity ^= 1;
-    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-    float mu[16], vc[16];
-    ld16(lane_addr, mu);
-    ld16(lane_addr + 16, vc);
-    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-    const int e = row0 + tid;
-    if (e < P.n) {
-        // a = clip(mu + exp(log_std) * eps): the Philox stream of the round-1 scalar kernel (seed, env id, launch counter), so the noise
-        // of an environment does not depend on the kernel that evaluates the network
-        const unsigned long long gid = P.env_offset + (unsigned long long)e;
-        float lp = 0.f;
-#pragma unroll
-        for (int o = 0; o < 12; o += 4) {
-            const U4 r = philox(P.seed ^ 0x504F4C4943590000ull, (unsigned)gid, (unsigned)(gid >> 32), (unsigned)P.counter, 0x50000000u + o);
-            const float a0 = sqrtf(-2.0f * logf(u01_open(r.x))), a1 = sqrtf(-2.0f * logf(u01_open(r.z)));
-            float s0, c0, s1, c1;
-            sincospif(2.0f * u01(r.y), &s0, &c0);
-            sincospif(2.0f * u01(r.w), &s1, &c1);
-            const float nz[4] = {a0 * c0, a0 * s0, a1 * c1, a1 * s1};
-#pragma unroll
-            for (int q = 0; q < 4; q++) {
-                float a = mu[o + q] + bias[256 + o + q];
-                if (P.log_std) {
-                    const float ls = bias[288 + o + q];
-                    a += expf(ls) * nz[q];
-                    lp += -0.5f * nz[q] * nz[q] - ls - 0.91893853320467274178f;     // log N(a; mu, sigma), before the clip (SB3 DiagGaussianDistribution.log_prob)
-                }
-                if (P.raw_act) P.raw_act[(size_t)e * 12 + o + q] = a;
-                P.act[(size_t)e * 12 + o + q] = fminf(bias[320 + o + q], fmaxf(bias[304 + o + q], a));
+                for (int k = 0; k < 64 / 8; k++)
+                    mma_tf32(tmem + 64, make_desc(s_hc + k * 256, 128, (64 / 4) * 128), make_desc(sbase + SM_W1C + k * 256, 128, (64 / 4) * 128), idesc, k > 0);
             }
+            commit(bar);
         }
-        if (P.logp) P.logp[e] = lp;
-        if (P.value) P.value[e] = vc[0] + bias[272];
+        mbar_wait(bar, parity); parity ^= 1;
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        hidden_epilogue(act, lane_addr, bias + 128, 0, critic ? 128 : 64, ltid);    // the layer-2 MMAs that read H1 have completed
+        handoff(g);
+
+        // ---- layer 3: columns 0..15 = H2a . W2a' (12 action means), columns 16..31 = H2c . W2c' (value in column 16)
+        if (ltid == 0) {
+            const uint32_t idesc = make_idesc_tf32(128, 16);
+#pragma unroll
+            for (int k = 0; k < 64 / 8; k++)
+                mma_tf32(tmem, make_desc(s_ha + k * 256, 128, (64 / 4) * 128), make_desc(sbase + SM_W2A + k * 256, 128, (64 / 4) * 128), idesc, k > 0);
+            if (critic) {
+#pragma unroll
+                for (int k = 0; k < 64 / 8; k++)
+                    mma_tf32(tmem + 16, make_desc(s_hc + k * 256, 128, (64 / 4) * 128), make_desc(sbase + SM_W2C + k * 256, 128, (64 / 4) * 128), idesc, k > 0);
+            }
+            commit(bar);
+        }
+        mbar_wait(bar, parity); parity ^= 1;
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        float mu[16], vc[16];
+        ld16(lane_addr, mu);
+        vc[0] = 0.f;
+        if (critic) ld16(lane_addr + 16, vc);
+        const int e = row0 + ltid;
+        if (e < P.n) {
+            // a = clip(mu + exp(log_std) * eps): the Philox stream of the scalar kernel (seed, env id, launch counter), so the noise
+            // of an environment does not depend on the kernel that evaluates the network
+            const unsigned long long gid = P.env_offset + (unsigned long long)e;
+            float lp = 0.f;
+            float out[12];
+#pragma unroll
+            for (int o = 0; o < 12; o += 4) {
+                float nz[4] = {0.f, 0.f, 0.f, 0.f};
+                if (P.log_std) {
+                    const U4 r = philox(P.seed ^ 0x504F4C4943590000ull, (unsigned)gid, (unsigned)(gid >> 32), (unsigned)P.counter, 0x50000000u + o);
+                    const float a0 = sqrtf(-2.0f * logf(u01_open(r.x))), a1 = sqrtf(-2.0f * logf(u01_open(r.z)));
+                    float s0, c0, s1, c1;
+                    sincospif(2.0f * u01(r.y), &s0, &c0);
+                    sincospif(2.0f * u01(r.w), &s1, &c1);
+                    nz[0] = a0 * c0; nz[1] = a0 * s0; nz[2] = a1 * c1; nz[3] = a1 * s1;
+                }
+#pragma unroll
+                for (int q = 0; q < 4; q++) {
+                    float a = mu[o + q] + bias[256 + o + q];
+                    if (P.log_std) {
+                        const float ls = bias[288 + o + q];
+                        a += expf(ls) * nz[q];
+                        lp += -0.5f * nz[q] * nz[q] - ls - 0.91893853320467274178f;     // log N(a; mu, sigma), before the clip (SB3 DiagGaussianDistribution.log_prob)
+                    }
+                    if (P.raw_act) P.raw_act[(size_t)e * 12 + o + q] = a;
+                    out[o + q] = fminf(bias[320 + o + q], fmaxf(bias[304 + o + q], a));
+                }
+            }
+            if (act_al) {
+#pragma unroll
+                for (int o = 0; o < 12; o += 4)
+                    *reinterpret_cast<float4*>(P.act + (size_t)e * 12 + o) = make_float4(out[o], out[o + 1], out[o + 2], out[o + 3]);
+            } else {
+#pragma unroll
+                for (int o = 0; o < 12; o++) P.act[(size_t)e * 12 + o] = out[o];
+            }
+            if (P.logp) P.logp[e] = lp;
+            if (P.value) P.value[e] = vc[0] + bias[272];
+        }
     }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
-    if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(tmem), "n"(128) : "memory");
+    if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(*tmem_slot), "n"(256) : "memory");
 }
 #endif  // !GO1_EMU
 

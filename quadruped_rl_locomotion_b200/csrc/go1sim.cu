@@ -1136,17 +1136,22 @@ static int launch_policy(go1_handle h, const Go1Policy* policy, const Go1Critic*
     GO1_LAUNCH(k_policy, n, 1, 0, s, obs_dev, act_dev, n, *policy, h->d_lo, h->d_hi, h->seed, h->launch_counter, h->env_offset);
 #else
     static bool attr_set = false;
+    static int sm_count[64] = {};
     if (!attr_set) {
         CK(cudaFuncSetAttribute(k_policy_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::SM_TOTAL));
         attr_set = true;
     }
+    const int dv = h->device >= 0 && h->device < 64 ? h->device : 0;
+    if (!sm_count[dv]) CK(cudaDeviceGetAttribute(&sm_count[dv], cudaDevAttrMultiProcessorCount, h->device));
     PolicyTCParams P;
     P.obs = obs_dev; P.act = act_dev; P.value = critic ? values_dev : nullptr; P.logp = logp_dev; P.raw_act = raw_dev; P.n = n;
     P.aw0 = policy->w0; P.ab0 = policy->b0; P.aw1 = policy->w1; P.ab1 = policy->b1; P.aw2 = policy->w2; P.ab2 = policy->b2; P.log_std = policy->log_std;
     P.cw0 = critic ? critic->w0 : nullptr; P.cb0 = critic ? critic->b0 : nullptr; P.cw1 = critic ? critic->w1 : nullptr;
     P.cb1 = critic ? critic->b1 : nullptr; P.cw2 = critic ? critic->w2 : nullptr; P.cb2 = critic ? critic->b2 : nullptr;
     P.lo = h->d_lo; P.hi = h->d_hi; P.seed = h->seed; P.counter = h->launch_counter; P.env_offset = h->env_offset;
-    k_policy_tc<<<(n + 127) / 128, 128, tc::SM_TOTAL, s>>>(P);
+    // persistent CTAs (one per SM, 1 resident by shared memory): two groups of four warps, each walking its own tiles of 128 rows
+    const int tiles = (n + 127) / 128;
+    if (tiles > 0) k_policy_tc<<<tiles < sm_count[dv] ? tiles : sm_count[dv], tc::THREADS, tc::SM_TOTAL, s>>>(P);
     CK(cudaGetLastError());
 #endif
     return GO1_OK;

@@ -48,7 +48,15 @@ constexpr int NDOF = 18;    // 0..5 trunk (3 lin world, 3 rot body frame), 6 + 3
 #ifndef GO1_PB_MASK
 #define GO1_PB_MASK 31         // which phase barriers exist: 1 F1 (before the pair collision), 2 F2 (after it), 4 B1 (before the Hessian),
 #endif                         // 8 B2 (before the factorisation), 16 B3 (before the line search); timing experiments only
-#if GO1_LOCKSTEP && GO1_PHASE_BARRIERS
+#if defined(GO1_PHASE_TIMING) && !defined(GO1_EMU)
+// Diagnostic build only (tools/phase_times.py): clock64 at every block barrier.  Bucket k holds the WORK a warp did since the
+// previous barrier (twork[k]) and the time it then WAITED at barrier k (twait[k]); k: 0 F1, 1 F2, 2 B1, 3 B2, 4 B3, 5 the
+// per-round barrier at the loop top, 6 the barrier at the start of a substep.
+#define GO1_PT_SYNC(k, stmt) do { const long long t0_ = clock64(); out.twork[k] += t0_ - out.tlast; stmt; const long long t1_ = clock64(); \
+                                  out.twait[k] += t1_ - t0_; out.tlast = t1_; } while (0)
+#define GO1_PT_K(bit) ((bit) == 1 ? 0 : (bit) == 2 ? 1 : (bit) == 4 ? 2 : (bit) == 8 ? 3 : 4)
+#define GO1_PBX(bit) do { if ((GO1_PB_MASK & (bit)) && (bit) <= 16) GO1_PT_SYNC(GO1_PT_K(bit), __syncthreads()); } while (0)
+#elif GO1_LOCKSTEP && GO1_PHASE_BARRIERS
 #define GO1_PBX(bit) do { if (GO1_PB_MASK & (bit)) __syncthreads(); } while (0)
 #else
 #define GO1_PBX(bit) ((void)0)
@@ -768,6 +776,10 @@ template <typename T> struct SubOut {
     T trunk_z;
     int ncon, iters, iters_total, overflow, bad;
     int nsub;                  // substeps completed in this control step
+#if defined(GO1_PHASE_TIMING) && !defined(GO1_EMU)
+    long long tlast, twork[7], twait[7];
+    int maxmode, rounds;
+#endif
 };
 
 template <typename T> struct Stage4 { T px[4], py[4], pz[4], d[4]; int n; };
@@ -1372,7 +1384,9 @@ GO1_NOINL void substep_w(const DevModel<T>& m, const EnvCfg<T>& cfg, WEnv<T>& E,
     DofRows<T> dr;
     dr.fr_aref = 0; dr.lim_s = 0; dr.lim_D = 0; dr.lim_aref = 0; dr.floss = 0; dr.Rf = 1;
     int ncon = 0;
-#if GO1_LOCKSTEP
+#if defined(GO1_PHASE_TIMING) && !defined(GO1_EMU)
+    GO1_PT_SYNC(6, __syncthreads());
+#elif GO1_LOCKSTEP
     __syncthreads();     // the warps of a block run the substep phases together: they share instruction fetches
 #endif
     if (active) {
@@ -1785,7 +1799,11 @@ GO1_NOINL void substep_w(const DevModel<T>& m, const EnvCfg<T>& cfg, WEnv<T>& E,
 #endif
 #pragma unroll 1
     while (true) {
-#if GO1_LOCKSTEP
+#if defined(GO1_PHASE_TIMING) && !defined(GO1_EMU)
+        bool all_conv_;
+        GO1_PT_SYNC(5, all_conv_ = __syncthreads_and(conv));
+        if (all_conv_) break;
+#elif GO1_LOCKSTEP
         if (__syncthreads_and(conv)) break;       // one Newton round per barrier, until every warp of the block converged
 #else
         if (conv) break;
@@ -1869,6 +1887,10 @@ GO1_NOINL void substep_w(const DevModel<T>& m, const EnvCfg<T>& cfg, WEnv<T>& E,
         __syncwarp();
         // robot-robot contacts (rare): inside one leg block, or leg-leg fill -> dense 12 x 12 leg block
         const int pmode = E.ncon > E.nfl ? pair_hessian(m, E, lane) : 0;
+#if defined(GO1_PHASE_TIMING) && !defined(GO1_EMU)
+        if ((pmode & 3) > out.maxmode) out.maxmode = pmode & 3;
+        out.rounds++;
+#endif
 #ifdef GO1_EMU_COUNT
         if (lane == 0) { __atomic_fetch_add(&g_emu_rounds[pmode & 3], 1, __ATOMIC_RELAXED); if (E.ncon > E.nfl) __atomic_fetch_add(&g_emu_rounds[3], 1, __ATOMIC_RELAXED); }
 #endif

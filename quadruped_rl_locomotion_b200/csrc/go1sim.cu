@@ -25,6 +25,9 @@
 #include <vector>
 
 #include "../../include/go1sim.h"
+#if defined(GO1_PHASE_TIMING) && !defined(GO1_EMU)
+namespace go1 { __device__ unsigned long long g_phase[5][16]; }     // diagnostic build only (tools/phase_times.py)
+#endif
 #include "go1_warp.cuh"
 
 #ifndef GO1_VARIANT      // timing variants (tools/build_variant.sh) may shrink the capacities
@@ -232,6 +235,10 @@ __global__ void __launch_bounds__(GO1_WARPS * 32, GO1_MINBLOCKS) k_step(const __
         if (!active) {      // keeps the block's barriers balanced
             SubOut<T> dummy;
             dummy.iters_total = 0; dummy.overflow = 0; dummy.bad = 0; dummy.nsub = 0; dummy.qacc = 0; dummy.qacc_prev = 0; dummy.qacc_prev2 = 0;
+#if defined(GO1_PHASE_TIMING) && !defined(GO1_EMU)
+            dummy.tlast = clock64(); dummy.maxmode = 0; dummy.rounds = 0;
+            for (int i = 0; i < 7; i++) { dummy.twork[i] = 0; dummy.twait[i] = 0; }
+#endif
             for (int s = 0; s < cfg.frame_skip; s++) substep_w(m, cfg, E, lane, dummy, false, (T*)nullptr, false);
             continue;
         }
@@ -272,6 +279,10 @@ __global__ void __launch_bounds__(GO1_WARPS * 32, GO1_MINBLOCKS) k_step(const __
             SubOut<T> out;
             out.iters_total = 0; out.overflow = 0; out.bad = 0; out.ncon = 0; out.iters = 0;
             out.qacc = 0; out.qfa = 0; out.qfc = 0; out.trunk_z = 0; out.qacc_prev = 0; out.qacc_prev2 = 0; out.nsub = 0;
+#if defined(GO1_PHASE_TIMING) && !defined(GO1_EMU)
+            out.tlast = clock64(); out.maxmode = 0; out.rounds = 0;
+            for (int i = 0; i < 7; i++) { out.twork[i] = 0; out.twait[i] = 0; }
+#endif
             const bool capture = P.diag_con != nullptr;
             T* con_out = capture ? P.diag_con + (size_t)env * DC_ENV : (T*)nullptr;
             {
@@ -293,6 +304,13 @@ __global__ void __launch_bounds__(GO1_WARPS * 32, GO1_MINBLOCKS) k_step(const __
                 substep_w(m, cfg, E, lane, out, capture && last, con_out, !out.bad,
                           (cfg.biped && last) ? P.bipk + (size_t)env * BK_N : (T*)nullptr);
             }
+#if defined(GO1_PHASE_TIMING) && !defined(GO1_EMU)
+            if (lane == 0) {
+                const int cls = (E.ncon > E.nfl && out.maxmode == 0) ? 1 : (out.maxmode == 0 ? 0 : out.maxmode + 1);     // 0 no pair rows, 1 inactive pair rows, 2 arrow, 3 pair-leg, 4 dense
+                for (int i = 0; i < 7; i++) { atomicAdd(&g_phase[cls][i], (unsigned long long)out.twork[i]); atomicAdd(&g_phase[cls][8 + i], (unsigned long long)out.twait[i]); }
+                atomicAdd(&g_phase[cls][7], 1ull); atomicAdd(&g_phase[cls][15], (unsigned long long)out.rounds);
+            }
+#endif
             if (out.bad) { out.qacc = 0; out.qfa = 0; out.qfc = 0; out.trunk_z = 0; }
             const bool legdof = lane >= 6 && lane < NDOF;
             const int jl = legdof ? lane - 6 : 0;
@@ -1415,3 +1433,13 @@ int go1_get_attr_f32(go1_handle h, const char* name, float* v) {
 long g_emu_rounds[4] = {0, 0, 0, 0};      // test-only instrumentation of the emulator build: Newton rounds by Hessian path
 extern "C" void go1_emu_round_counts(long* out) { for (int i = 0; i < 4; i++) out[i] = g_emu_rounds[i]; }
 #endif
+
+#if defined(GO1_PHASE_TIMING) && !defined(GO1_EMU)
+// diagnostic build only: reads and clears the per-class phase clocks (tools/phase_times.py)
+extern "C" int go1_debug_phase_times(unsigned long long* out80) {
+    if (cudaMemcpyFromSymbol(out80, go1::g_phase, sizeof(unsigned long long) * 80) != cudaSuccess) return GO1_ECUDA;
+    unsigned long long z[80] = {};
+    return cudaMemcpyToSymbol(go1::g_phase, z, sizeof(z)) == cudaSuccess ? GO1_OK : GO1_ECUDA;
+}
+#endif
+

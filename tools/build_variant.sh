@@ -4,6 +4,7 @@
 set -e
 cd "$(dirname "$0")/.."
 name=$1; shift
+mkdir -p tools/variants
 nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -Xcompiler -fPIC -shared --expt-relaxed-constexpr \
   -prec-div=false -prec-sqrt=false -ftz=true -DGO1_VARIANT "$@" -o tools/variants/libgo1sim_$name.so quadruped_rl_locomotion_b200/csrc/go1sim.cu
 echo built tools/variants/libgo1sim_$name.so

@@ -222,7 +222,8 @@ int go1_rollout(go1_handle h, int n_steps, int action_mode, const Go1Policy* pol
  * (go1_mujoco_env.py:487-493) of every currently unhealthy environment to a Philox draw in [0, max_unhealthy_steps], so that episode ends
  * (and the auto-reset path) arrive at a uniform rate.  Physics state untouched. */
 int go1_stagger_phases(go1_handle h);
-/* elapsed device time (ms, CUDA events on the launch stream) and kernel launches of the last go1_rollout */
+/* elapsed device time (ms, CUDA events on the launch stream) and kernel launches of the last go1_rollout (per control step:
+ * k_order + k_step, + the policy kernel in GO1_ACTION_POLICY mode) */
 int go1_last_rollout_timing(go1_handle h, float* ms, int* launches);
 
 /* Actor forward + action sampling for n rows of observations (device pointers): replaces the SB3

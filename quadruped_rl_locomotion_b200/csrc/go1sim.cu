@@ -1117,7 +1117,7 @@ int go1_rollout(go1_handle h, int n_steps, int action_mode, const Go1Policy* pol
         h->launch_counter++;
         int rc = launch(h, P, s);
         if (rc != GO1_OK) return rc;
-        launches++;
+        launches += 2;      // k_order + k_step
     }
     CK(cudaEventRecord(h->ev1, s));
     CK(cudaStreamSynchronize(s));

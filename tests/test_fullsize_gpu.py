@@ -74,7 +74,7 @@ def test_device_statistics_match_outputs(cuda_lib_f32):
     a = Sim(blob, n, lib=cuda_lib_f32, seed=3); b = Sim(blob, n, lib=cuda_lib_f32, seed=3)
     a.reset_host(); b.reset_host()
     st = a.rollout(4, ACTION_RANDOM, None)
-    assert st["env_steps"] == 4 * n and st["launches"] == 4 and st["n_bad_state"] == 0
+    assert st["env_steps"] == 4 * n and st["launches"] == 8 and st["n_bad_state"] == 0
     tot = 0.0
     for _ in range(4):
         s1 = b.rollout(1, ACTION_RANDOM, None)

@@ -39,11 +39,13 @@ struct PolicyTCParams {
 namespace tc {
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-// fp32 -> tf32 with round-to-nearest (the tensor core itself TRUNCATES the low 13 mantissa bits: biased, twice the error)
+// fp32 -> tf32 with round-to-nearest, ties away from zero (what cvt.rna.tf32.f32 does; the tensor core itself TRUNCATES the low 13
+// mantissa bits: biased, twice the error).  cvt.rna.tf32 issues at a fraction of the ALU rate and was 27 % of the kernel's stall
+// samples; adding half an ulp of the dropped bits to the magnitude is one integer add, and the MMA ignores the low bits anyway.
+__device__ __forceinline__ float to_tf32_finite(float x) { return __uint_as_float(__float_as_uint(x) + 0x1000u); }      // |x| finite (tanh outputs)
 __device__ __forceinline__ float to_tf32(float x) {
-    uint32_t r;
-    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
-    return __uint_as_float(r);
+    const uint32_t u = __float_as_uint(x);
+    return __uint_as_float((u & 0x7F800000u) == 0x7F800000u ? u : u + 0x1000u);      // inf / nan pass through
 }
 
 // shared-memory matrix descriptor (cute::UMMA::SmemDescriptor): start address >> 4 in [0,14), leading byte offset >> 4 in
@@ -144,8 +146,8 @@ __device__ __forceinline__ void hidden_epilogue(unsigned char* act, uint32_t lan
         for (int q = 0; q < 4; q++) {
             const int col = (c0 & 63) + 4 * q;
             float4 o;
-            o.x = to_tf32(tanh_fast(v[4 * q + 0] + bias[c0 + 4 * q + 0])); o.y = to_tf32(tanh_fast(v[4 * q + 1] + bias[c0 + 4 * q + 1]));
-            o.z = to_tf32(tanh_fast(v[4 * q + 2] + bias[c0 + 4 * q + 2])); o.w = to_tf32(tanh_fast(v[4 * q + 3] + bias[c0 + 4 * q + 3]));
+            o.x = to_tf32_finite(tanh_fast(v[4 * q + 0] + bias[c0 + 4 * q + 0])); o.y = to_tf32_finite(tanh_fast(v[4 * q + 1] + bias[c0 + 4 * q + 1]));
+            o.z = to_tf32_finite(tanh_fast(v[4 * q + 2] + bias[c0 + 4 * q + 2])); o.w = to_tf32_finite(tanh_fast(v[4 * q + 3] + bias[c0 + 4 * q + 3]));
             *reinterpret_cast<float4*>(dst + (col >> 2) * 128) = o;
         }
     }
@@ -201,18 +203,27 @@ __global__ void __launch_bounds__(tc::THREADS, 1) k_policy_tc(const __grid_const
     const bool obs_al = (reinterpret_cast<uintptr_t>(P.obs) & 15) == 0, act_al = (reinterpret_cast<uintptr_t>(P.act) & 15) == 0;
     uint32_t parity = 0;
 
+    // this thread's 12 float4 of a tile's observations (float4 number i = ltid + 128 j): loaded one tile ahead, so the global-memory
+    // latency hides behind the three MMA / epilogue phases of the tile before
+    float4 pre[12];
+    auto load_tile = [&](int tile) {
+        const int row0 = tile * 128;
+#pragma unroll
+        for (int j = 0; j < 12; j++) {
+            int r, kc;
+            unit_rc<48>(ltid + 128 * j, r, kc);
+            pre[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (tile < tiles && row0 + r < P.n) pre[j] = load4(P.obs + (size_t)(row0 + r) * 48 + 4 * kc, obs_al);
+        }
+    };
+    load_tile(blockIdx.x + g * gridDim.x);
 #pragma unroll 1
     for (int tile = blockIdx.x + g * gridDim.x; tile < tiles; tile += 2 * gridDim.x) {
         const int row0 = tile * 128;
-        // observations of this tile: 16-byte global reads, linear 16-byte shared-memory stores (the region doubles as HA later)
-#pragma unroll 4
-        for (int i = ltid; i < 128 * (48 / 4); i += 128) {
-            int r, kc;
-            unit_rc<48>(i, r, kc);
-            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (row0 + r < P.n) v = tf32x4(load4(P.obs + (size_t)(row0 + r) * 48 + 4 * kc, obs_al));
-            *reinterpret_cast<float4*>(act + 16 * i) = v;
-        }
+        // observations of this tile: linear 16-byte shared-memory stores (the region doubles as HA later), then the next tile's loads
+#pragma unroll
+        for (int j = 0; j < 12; j++) *reinterpret_cast<float4*>(act + 16 * (ltid + 128 * j)) = tf32x4(pre[j]);
+        load_tile(tile + 2 * gridDim.x);
         handoff(g);      // also orders the previous tile's TMEM reads before this tile's MMAs
 
         // ---- layer 1: D[128 x 128] = obs[128 x 48] . [W0a; W0c]'

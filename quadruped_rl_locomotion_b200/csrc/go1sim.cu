@@ -506,7 +506,17 @@ __global__ void __launch_bounds__(GO1_WARPS * 32, GO1_MINBLOCKS) k_step(const __
                 // in one group: the pair phases of a Newton round (pair Hessian, coupled-leg factorisation) then run in blocks whose
                 // warps mostly all need them, and the other blocks never wait for them.
                 {
+#if !defined(GO1_WORK_KEY) || GO1_WORK_KEY == 3
+                    // inside a level: by the number of robot-robot contacts, then floor contacts (the per-phase cost of a round follows
+                    // the row counts; measured 2 % better than the iteration-based key, profiles/r2_experiments.md section 3)
+                    int w = 8 * (E.ncon - E.nfl) + E.nfl;
+#elif GO1_WORK_KEY == 0      // timing experiments only: other orders inside a level
                     int w = (out.iters_total + 2 * out.ncon) >> 1;
+#elif GO1_WORK_KEY == 1
+                    int w = 4 * out.ncon + (out.iters_total >> 4);
+#elif GO1_WORK_KEY == 2
+                    int w = out.iters_total;
+#endif
                     w = w > 63 ? 63 : w;
 #ifndef GO1_NO_PAIR_SORT
                     // level 0: floor contacts only; 1: robot-robot contacts inside one leg / with the trunk; 2: between two legs

@@ -519,14 +519,20 @@ __global__ void __launch_bounds__(GO1_WARPS * 32, GO1_MINBLOCKS) k_step(const __
 #endif
                     w = w > 63 ? 63 : w;
 #ifndef GO1_NO_PAIR_SORT
-                    // level 0: floor contacts only; 1: robot-robot contacts inside one leg / with the trunk; 2: between two legs
+                    // level 0: floor contacts only; 1: robot-robot contacts inside one leg / with the trunk; 2: between ONE pair of legs
+                    // (6x6 path); 3: between several pairs (dense path)
                     int lvl = 0;
+                    int code0 = -1;
                     if (!out.bad)
                         for (int c = E.nfl; c < E.ncon; c++) {
                             const int mt = E.c_meta[c];
                             const int b2 = meta_b2(mt), b1 = meta_b1p(mt) - 1;
                             const bool cross = b1 >= 1 && b2 >= 1 && (b1 - 1) / 3 != (b2 - 1) / 3;
-                            lvl = cross ? 2 : (lvl > 1 ? lvl : 1);
+                            if (cross) {
+                                const int l1 = (b1 - 1) / 3, l2 = (b2 - 1) / 3, code = l1 < l2 ? 4 * l1 + l2 : 4 * l2 + l1;
+                                if (code0 < 0) code0 = code;
+                                lvl = code != code0 ? 3 : (lvl > 2 ? lvl : 2);
+                            } else lvl = lvl > 1 ? lvl : 1;
                         }
                     w += 64 * lvl;
 #endif

@@ -1169,14 +1169,12 @@ static int launch_policy(go1_handle h, const Go1Policy* policy, const Go1Critic*
     (void)critic; (void)values_dev; (void)logp_dev; (void)raw_dev;
     GO1_LAUNCH(k_policy, n, 1, 0, s, obs_dev, act_dev, n, *policy, h->d_lo, h->d_hi, h->seed, h->launch_counter, h->env_offset);
 #else
-    static bool attr_set = false;
-    static int sm_count[64] = {};
-    if (!attr_set) {
-        CK(cudaFuncSetAttribute(k_policy_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::SM_TOTAL));
-        attr_set = true;
-    }
+    static int sm_count[64] = {};       // per device ordinal; 0 = this device has not been set up yet
     const int dv = h->device >= 0 && h->device < 64 ? h->device : 0;
-    if (!sm_count[dv]) CK(cudaDeviceGetAttribute(&sm_count[dv], cudaDevAttrMultiProcessorCount, h->device));
+    if (!sm_count[dv]) {                // function attributes are per device: once on each device that launches the kernel
+        CK(cudaFuncSetAttribute(k_policy_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::SM_TOTAL));
+        CK(cudaDeviceGetAttribute(&sm_count[dv], cudaDevAttrMultiProcessorCount, h->device));
+    }
     PolicyTCParams P;
     P.obs = obs_dev; P.act = act_dev; P.value = critic ? values_dev : nullptr; P.logp = logp_dev; P.raw_act = raw_dev; P.n = n;
     P.aw0 = policy->w0; P.ab0 = policy->b0; P.aw1 = policy->w1; P.ab1 = policy->b1; P.aw2 = policy->w2; P.ab2 = policy->b2; P.log_std = policy->log_std;

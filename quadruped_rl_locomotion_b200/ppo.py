@@ -228,12 +228,16 @@ class DevicePPO:
         lo, hi = self.sim.action_bounds()
         self.lo, self.hi = torch.from_numpy(lo).to(self.device), torch.from_numpy(hi).to(self.device)
         self._started = False
+        # ONE stream for the whole rollout, the library's kernels and torch's ops alike.  It must not be torch's default stream: the
+        # C ABI reads a NULL stream as "the handle's own stream" (non-blocking), on which the policy / step kernels would run
+        # unordered with torch's copies of their outputs.
+        self.stream = torch.cuda.Stream(device=self.device) if self.device.type == "cuda" else None
 
     # -- policy forward for all environments: one tcgen05 kernel (actions, raw samples, values)
     def _act(self):
         if self.use_tc:
             pol, cri = self.net.kernel_pointers()
-            self.sim.policy_forward(pol, cri, self.obs, self.act, self.val, None, stream=torch.cuda.current_stream().cuda_stream, raw_act=self.raw)
+            self.sim.policy_forward(pol, cri, self.obs, self.act, self.val, None, stream=self.stream.cuda_stream, raw_act=self.raw)
         else:
             mu = self.net.mean(self.obs)
             self.raw.copy_(mu + self.net.log_std.exp() * torch.randn_like(mu))
@@ -241,8 +245,16 @@ class DevicePPO:
             self.val.copy_(self.net.value(self.obs))
 
     def collect_rollouts(self):
+        self.stream.wait_stream(torch.cuda.current_stream(self.device))      # the optimiser's last update is visible to the rollout
+        with torch.cuda.stream(self.stream):
+            out = self._collect()
+        torch.cuda.current_stream(self.device).wait_stream(self.stream)      # ... and the batch to the update
+        return out
+
+    def _collect(self):
         hp, B = self.hp, self.buf
-        stream = torch.cuda.current_stream().cuda_stream
+        stream = self.stream.cuda_stream
+        assert stream != 0
         if not self._started:
             self.sim.reset(None, self.obs, stream)
             self._started = True

@@ -180,6 +180,32 @@ def test_shipped_final_model_zip_loads():
 
 
 @pytest.mark.gpu
+def test_rollout_buffers_belong_to_their_observations(cuda_lib_f32):
+    """What collect_rollouts stores at step t (values, unclipped samples) must be what the kernels computed FROM the observations of
+    step t.  (The library reads a NULL stream as "the handle's own stream"; a rollout that passes torch's default stream stores the
+    outputs of the PREVIOUS step, and training silently degenerates.)"""
+    from quadruped_rl_locomotion_b200.vec_env import Go1CudaVecEnv
+    env = Go1CudaVecEnv(4096, ctrl_type="position", library=cuda_lib_f32, seed=3)
+    m = ppo.DevicePPO(env, n_steps=6, seed=0)
+    with torch.no_grad():
+        m.net.action_net.weight.mul_(60.0)                  # means that move with the observation (the SB3 init has gain 0.01)
+        m.net.log_std.fill_(-1.0)
+    batch, _ = m.collect_rollouts()
+    torch.cuda.synchronize()
+    B = m.buf
+    with torch.no_grad():
+        for t in range(6):
+            v = m.net.value(B["obs"][t])
+            assert (B["val"][t] - v).abs().max().item() < 2e-2, t                          # tf32 forward vs fp32
+            eps = (B["raw"][t] - m.net.mean(B["obs"][t])) / m.net.log_std.exp()
+            assert abs(eps.std().item() - 1.0) < 0.05 and abs(eps.mean().item()) < 0.02, (t, eps.std().item())
+        # two consecutive steps see different observations, so a one-step lag would show in both checks
+        assert (m.net.value(B["obs"][1]) - m.net.value(B["obs"][0])).abs().mean().item() > 0.05
+        assert (m.net.mean(B["obs"][1]) - m.net.mean(B["obs"][0])).abs().mean().item() > 0.05
+    env.close()
+
+
+@pytest.mark.gpu
 def test_device_ppo_learns_and_round_trips(cuda_lib_f32, tmp_path):
     """A few iterations of the whole loop on the GPU (tcgen05 policy forward in the rollout), then save / load / predict."""
     from quadruped_rl_locomotion_b200.vec_env import Go1CudaVecEnv

@@ -25,7 +25,10 @@
  * Conventions: every function returns 0 on success or a negative GO1_E* code; the message is
  * available from go1_last_error().  No exceptions cross the ABI.  One handle = one GPU = one host
  * thread at a time.  Device-pointer arguments are raw CUDA device pointers (e.g. torch
- * tensor.data_ptr()); `stream` is a cudaStream_t cast to void* (NULL = the handle's own stream).
+ * tensor.data_ptr()); `stream` is a cudaStream_t cast to void*.  NULL = the handle's own stream, which is NON-BLOCKING: it is not
+ * the legacy default stream and does not synchronise with it.  A caller whose own GPU work produces the inputs or consumes the
+ * outputs passes the stream that work runs on (from PyTorch: a torch.cuda.Stream(); the default stream's handle is 0 = NULL) or
+ * synchronises around the call.
  * Per-environment numerical failure is not an error: the env is flagged, auto-reset and counted.
  */
 #ifndef GO1SIM_H_

@@ -70,11 +70,12 @@ def test_policy_act_gpu(cuda_lib_f32):
     torch.backends.cuda.matmul.allow_tf32 = False
     h = torch.tanh(obs @ dev[0].T + dev[1]); h = torch.tanh(h @ dev[2].T + dev[3])
     ref = torch.minimum(torch.maximum(h @ dev[4].T + dev[5], torch.from_numpy(lo).cuda()), torch.from_numpy(hi).cuda())
+    torch.cuda.synchronize()            # the library runs on the handle's own stream: torch's fills / copies above must have landed
     # (1) the fp32 scalar kernel
     sim.policy_act_scalar(det, obs, act, n=n); torch.cuda.synchronize()
     assert (act - ref).abs().max().item() < TOL
     # (2) the tensor-core kernel (the product path: go1_policy_act, go1_rollout(GO1_ACTION_POLICY))
-    act_tc = torch.zeros(n, 12, device="cuda")
+    act_tc = torch.zeros(n, 12, device="cuda"); torch.cuda.synchronize()
     sim.policy_act(det, obs, act_tc, n=n); torch.cuda.synchronize()
     err = (act_tc - ref).abs()
     print("tcgen05 tf32 policy: max |action - fp32 reference| = %.2e, mean %.2e" % (err.max().item(), err.mean().item()))
@@ -86,6 +87,7 @@ def test_policy_act_gpu(cuda_lib_f32):
     ls = torch.full((12,), -1.0, device="cuda")
     sto = Policy(*[t.data_ptr() for t in z], ls.data_ptr())
     o0 = torch.zeros(n, 48, device="cuda"); a = torch.zeros(n, 12, device="cuda")
+    torch.cuda.synchronize()
     big.policy_act(sto, o0, a, n=n); torch.cuda.synchronize()
     s = float(np.exp(-1.0))
     assert abs(a.mean().item()) < 0.01 and abs(a.std().item() - s) < 0.01
@@ -94,6 +96,7 @@ def test_policy_act_gpu(cuda_lib_f32):
     # the noise stream does not depend on which kernel evaluates the network: same seed / counter -> same sample up to the tf32 mean
     big2 = Sim(pc.model_blob("torque"), 64, lib=cuda_lib_f32, seed=9)
     a2 = torch.zeros(n, 12, device="cuda")
+    torch.cuda.synchronize()
     big2.policy_act_scalar(sto, o0, a2, n=n); torch.cuda.synchronize()
     assert (a - a2).abs().max().item() < 1e-6
     big.close(); big2.close(); sim.close()
@@ -120,6 +123,7 @@ def test_policy_forward_actor_critic_gpu(cuda_lib_f32):
     cri = Critic(*[t.data_ptr() for t in cw])
     obs = torch.from_numpy(_obs(n, seed=5)[n // 8:]).cuda().contiguous(); n = obs.shape[0]
     act = torch.zeros(n, 12, device="cuda"); val = torch.zeros(n, device="cuda"); lp = torch.zeros(n, device="cuda")
+    torch.cuda.synchronize()
     sim.policy_forward(pol, cri, obs, act, val, lp, n=n); torch.cuda.synchronize()
     torch.backends.cuda.matmul.allow_tf32 = False
     h = torch.tanh(obs @ dev[0].T + dev[1]); h = torch.tanh(h @ dev[2].T + dev[3]); mu = h @ dev[4].T + dev[5]
@@ -139,6 +143,7 @@ def test_policy_forward_actor_critic_gpu(cuda_lib_f32):
     # critic == NULL leaves the value buffer alone; deterministic actor returns the mean
     val2 = torch.full((n,), 7.0, device="cuda"); act2 = torch.zeros(n, 12, device="cuda")
     det = Policy(*[d.data_ptr() for d in dev[:6]], None)
+    torch.cuda.synchronize()
     sim.policy_forward(det, None, obs, act2, val2, None, n=n); torch.cuda.synchronize()
     assert torch.all(val2 == 7.0)
     assert (act2 - torch.minimum(torch.maximum(mu, lo_t), hi_t)).abs().max().item() < TOL_TF32

@@ -82,7 +82,7 @@ def test_camera_tracks_the_robot_and_scene_structure(cuda_lib_f32):
     assert (grey ^ grey2).sum() > 0.05 * grey.sum()
     # device output buffer + several environments in one launch
     import torch
-    out = torch.zeros(2, 96, 128, 3, dtype=torch.uint8, device="cuda")
+    out = torch.zeros(2, 96, 128, 3, dtype=torch.uint8, device="cuda"); torch.cuda.synchronize()
     env.sim.render((0, 1), 128, 96, out=out)
     assert out.float().std().item() > 5
     env.close()

@@ -40,6 +40,9 @@ POLICIES = {
     # position control, rand_power 1); policy_ppo_b200.npz is committed.  Evaluated in the reference env like the shipped ones
     # ("eval of the trained policy in both simulators").
     "ppo_b200": None,
+    # the same in round 2: DevicePPO, 240 M steps, position control, rand_power 0, on the simulator WITH robot-robot contacts
+    # (profiles/r2_ppo_240M_steps_16384envs.log); policy_ppo_b200_r2.npz is committed
+    "ppo_b200_r2": None,
 }
 V_DES = (0.5, 0.0, 0.0)
 RAND_POWER = 1.0     # reset joint noise N(0, 0.1 rad) (go1_mujoco_env.py:974-982): without it every upright episode of a

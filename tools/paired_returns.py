@@ -3,7 +3,7 @@ draws or a real difference?  A walking policy is a contraction, so from IDENTICA
 the same episodes; this tool runs the CUDA simulator from the reference env's own reset states (same seeds as the fixture) and
 compares the returns episode by episode.
 
-    python tools/paired_returns.py gen [n=2000]         # here (needs /root/reference): reset states -> tools/scratch/reset_states.npz
+    python tools/paired_returns.py gen [tag]            # here (needs /root/reference): reset states of the fixture's seeds -> tools/scratch/reset_states.npz
     python tools/paired_returns.py run <tag> [f32|f64]  # on the GPU box"""
 import os
 import sys
@@ -15,17 +15,19 @@ sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tests")); sys.p
 OUT = os.path.join(ROOT, "tools", "scratch", "reset_states.npz")
 
 
-def gen(n):
+def gen(tag):
+    """Reset states of ALL seeds of the fixture of `tag` (the reset does not depend on the policy, only on the seed)."""
     import make_returns as mr
     from oracle.ref_env import make_reference_env
+    seeds = np.load(os.path.join(ROOT, "tests", "golden", f"returns_{tag}.npz"))["seed"].astype(int)
     env = make_reference_env("position", rand_power=mr.RAND_POWER)
     env._desired_velocity_min = np.array(mr.V_DES); env._desired_velocity_max = np.array(mr.V_DES)
     qpos, obs0 = [], []
-    for s in range(1000, 1000 + n):
-        np.random.seed(s)
+    for s in seeds:
+        np.random.seed(int(s))
         o, _ = env.reset()
         qpos.append(env.data.qpos.copy()); obs0.append(o.copy())
-    np.savez(OUT, seed=np.arange(1000, 1000 + n), qpos=np.array(qpos), obs0=np.array(obs0))
+    np.savez(OUT, seed=seeds, qpos=np.array(qpos, np.float64), obs0=np.array(obs0, np.float32))
     print("wrote", OUT, len(qpos))
 
 
@@ -44,7 +46,7 @@ def run(tag, prec):
         env.sim.set_state(e, qpos=st["qpos"][e], qvel=np.zeros(18), qacc_warmstart=np.zeros(18))
     act = tpr._policy(tag)
     lo, hi = env.action_space.low, env.action_space.high
-    obs = st["obs0"].copy()
+    obs = st["obs0"].astype(np.float64)
     ret = np.zeros(n); length = np.zeros(n, int); alive = np.ones(n, bool)
     for _ in range(int(ref["max_steps"])):
         obs, rew, dones, _ = env.step(act(obs, lo, hi))
@@ -67,6 +69,6 @@ def run(tag, prec):
 
 if __name__ == "__main__":
     if sys.argv[1] == "gen":
-        gen(int(sys.argv[2]) if len(sys.argv) > 2 else 2000)
+        gen(sys.argv[2] if len(sys.argv) > 2 else "ppo_b200")
     else:
         run(sys.argv[2], sys.argv[3] if len(sys.argv) > 3 else "f32")

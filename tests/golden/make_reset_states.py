@@ -3,7 +3,7 @@ the first 4096 seeds of the return fixtures (``make_returns.py``: ``np.random.se
 the policy).  ``tests/test_policy_returns.py`` starts the CUDA simulator from exactly these states, which removes the sampling
 noise of the reset draws from the comparison of the mean returns.
 
-    python tests/golden/make_reset_states.py [n=4096]"""
+    python tests/golden/make_reset_states.py [n=4096] [output.npz]"""
 import os
 import sys
 
@@ -25,9 +25,10 @@ def main():
         np.random.seed(int(s))
         o, _ = env.reset()
         qpos.append(env.data.qpos.copy()); obs0.append(o.copy())
-    np.savez_compressed(os.path.join(mr.OUT, "reset_states_pos.npz"), seed=seeds, qpos=np.array(qpos, np.float64), obs0=np.array(obs0, np.float64),
+    out = sys.argv[2] if len(sys.argv) > 2 else os.path.join(mr.OUT, "reset_states_pos.npz")
+    np.savez_compressed(out, seed=seeds, qpos=np.array(qpos, np.float64), obs0=np.array(obs0, np.float64),
                         rand_power=mr.RAND_POWER, v_des=np.array(mr.V_DES))
-    print("wrote reset_states_pos.npz", len(seeds))
+    print("wrote", out, len(seeds))
 
 
 if __name__ == "__main__":

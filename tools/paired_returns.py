@@ -3,8 +3,10 @@ draws or a real difference?  A walking policy is a contraction, so from IDENTICA
 the same episodes; this tool runs the CUDA simulator from the reference env's own reset states (same seeds as the fixture) and
 compares the returns episode by episode.
 
-    python tools/paired_returns.py gen [tag]            # here (needs /root/reference): reset states of the fixture's seeds -> tools/scratch/reset_states.npz
-    python tools/paired_returns.py run <tag> [f32|f64]  # on the GPU box"""
+    python tests/golden/make_reset_states.py 12000 tools/scratch/reset_states.npz   # here (needs /root/reference); optional: all fixture seeds
+    python tools/paired_returns.py run <tag> [f32|f64]                              # on the GPU box
+
+Without tools/scratch/reset_states.npz the 4096 committed states of tests/golden/reset_states_pos.npz are used."""
 import os
 import sys
 
@@ -13,22 +15,8 @@ import numpy as np
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tests")); sys.path.insert(0, os.path.join(ROOT, "tests", "golden"))
 OUT = os.path.join(ROOT, "tools", "scratch", "reset_states.npz")
-
-
-def gen(tag):
-    """Reset states of ALL seeds of the fixture of `tag` (the reset does not depend on the policy, only on the seed)."""
-    import make_returns as mr
-    from oracle.ref_env import make_reference_env
-    seeds = np.load(os.path.join(ROOT, "tests", "golden", f"returns_{tag}.npz"))["seed"].astype(int)
-    env = make_reference_env("position", rand_power=mr.RAND_POWER)
-    env._desired_velocity_min = np.array(mr.V_DES); env._desired_velocity_max = np.array(mr.V_DES)
-    qpos, obs0 = [], []
-    for s in seeds:
-        np.random.seed(int(s))
-        o, _ = env.reset()
-        qpos.append(env.data.qpos.copy()); obs0.append(o.copy())
-    np.savez(OUT, seed=seeds, qpos=np.array(qpos, np.float64), obs0=np.array(obs0, np.float32))
-    print("wrote", OUT, len(qpos))
+if not os.path.exists(OUT):
+    OUT = os.path.join(ROOT, "tests", "golden", "reset_states_pos.npz")
 
 
 def run(tag, prec):
@@ -36,6 +24,7 @@ def run(tag, prec):
     from quadruped_rl_locomotion_b200.lib import Go1Lib
     from quadruped_rl_locomotion_b200.vec_env import Go1CudaVecEnv
     st = np.load(OUT)
+    sel = None
     ref = np.load(os.path.join(ROOT, "tests", "golden", f"returns_{tag}.npz"))
     idx = {int(s): i for i, s in enumerate(ref["seed"])}
     n = len(st["seed"])
@@ -68,7 +57,4 @@ def run(tag, prec):
 
 
 if __name__ == "__main__":
-    if sys.argv[1] == "gen":
-        gen(sys.argv[2] if len(sys.argv) > 2 else "ppo_b200")
-    else:
-        run(sys.argv[2], sys.argv[3] if len(sys.argv) > 3 else "f32")
+    run(sys.argv[2], sys.argv[3] if len(sys.argv) > 3 else "f32")

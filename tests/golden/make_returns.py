@@ -41,7 +41,7 @@ POLICIES = {
     # ("eval of the trained policy in both simulators").
     "ppo_b200": None,
     # the same in round 2: DevicePPO, 240 M steps, position control, rand_power 0, on the simulator WITH robot-robot contacts
-    # (profiles/r2_ppo_240M_steps_16384envs.log); policy_ppo_b200_r2.npz is committed
+    # (profiles/r2_ppo_700M_steps_16384envs.log); policy_ppo_b200_r2.npz is committed
     "ppo_b200_r2": None,
 }
 V_DES = (0.5, 0.0, 0.0)
